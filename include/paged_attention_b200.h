@@ -1,0 +1,231 @@
+/*
+ * paged_attention_b200.h -- C ABI of libpaged_b200.so
+ *
+ * B200 (sm_100a) implementation of vLLM v0.1.0's PagedAttention decode path:
+ * the decode-attention operator and the KV-cache movers.  Every entry point
+ * below replaces one pybind11-bound function of the reference; the citation
+ * after "replaces:" is the reference interface it is a drop-in for
+ * (paths relative to the reference tree).
+ *
+ * Conventions
+ *   - plain pointers and sizes only; no torch / ATen types;
+ *   - all device pointers belong to the CUDA device that is current when the
+ *     call is made; work is enqueued on `stream` (a cudaStream_t passed as
+ *     void*; NULL = the legacy default stream) and the call returns without
+ *     synchronising the host;
+ *   - every function returns PA_OK (0) or a negative PA_ERR_* code;
+ *     pa_last_error() then returns a thread-local, NUL-terminated message;
+ *   - the caller owns every buffer.  The only state kept by the library is a
+ *     per-(device, stream) scratch buffer for split-context partial results
+ *     (see pa_release_workspaces).
+ *
+ * Data layout (reference: vllm/worker/cache_engine.py:48-63,
+ * csrc/cache_kernels.cu:165-178), with x = 16 / sizeof(T):
+ *   key_cache   [num_blocks][num_heads][head_size / x][block_size][x]
+ *   value_cache [num_blocks][num_heads][head_size][block_size]
+ * A "page" is the contiguous (block, head) slice of either cache:
+ * head_size * block_size * sizeof(T) bytes.
+ */
+#ifndef PAGED_ATTENTION_B200_H_
+#define PAGED_ATTENTION_B200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PA_ABI_VERSION 1
+
+#if defined(__GNUC__) || defined(__clang__)
+#define PA_API __attribute__((visibility("default")))
+#else
+#define PA_API
+#endif
+
+/* element type of q / k / v / out and both caches */
+enum pa_dtype {
+  PA_F16 = 0,  /* IEEE binary16  (torch.half)     */
+  PA_BF16 = 1, /* bfloat16       (torch.bfloat16) */
+  PA_F32 = 2   /* IEEE binary32  (torch.float)    */
+};
+
+/* direction of pa_swap_blocks */
+enum pa_copy_kind {
+  PA_COPY_D2D = 0, /* both caches on the current device */
+  PA_COPY_D2H = 1, /* swap-out: GPU cache -> host cache */
+  PA_COPY_H2D = 2  /* swap-in : host cache -> GPU cache */
+};
+
+enum pa_status {
+  PA_OK = 0,
+  PA_ERR_UNSUPPORTED_HEAD_SIZE = -1,  /* head_size not in {64, 80, 96, 128}  */
+  PA_ERR_UNSUPPORTED_BLOCK_SIZE = -2, /* block_size not in {8, 16, 32}       */
+  PA_ERR_UNSUPPORTED_DTYPE = -3,
+  PA_ERR_INVALID_ARGUMENT = -4, /* NULL pointer, negative size, misalignment */
+  PA_ERR_CUDA = -5              /* a CUDA runtime call failed                */
+};
+
+/* ------------------------------------------------------------------------ */
+/* library                                                                  */
+/* ------------------------------------------------------------------------ */
+
+PA_API int pa_abi_version(void);
+
+/* Message of the last failed call made by the calling thread ("" if none). */
+PA_API const char* pa_last_error(void);
+
+/* Compute capability the kernels were compiled for (100 -> sm_100a). */
+PA_API int pa_compiled_sm(void);
+
+/* Number of kernels launched by this library since load (all threads).
+ * bench.py reads it before/after the timed region ("gpu_launches"). */
+PA_API uint64_t pa_launch_count(void);
+
+/* Frees every split-context scratch buffer held for the current device.
+ * Synchronises the device.  Safe to call at any time. */
+PA_API int pa_release_workspaces(void);
+
+/* ------------------------------------------------------------------------ */
+/* decode attention                                                         */
+/* ------------------------------------------------------------------------ */
+
+/*
+ * replaces: attention_ops.single_query_cached_kv_attention
+ *           csrc/attention.cpp:3-19, csrc/attention/attention_kernels.cu:450-469
+ *           (launcher :332-401, kernel :67-314)
+ *
+ * For every sequence i < num_seqs and head h < num_heads:
+ *   out[i][h][:] = softmax(scale * q[i][h][:] . K[i][h]^T) . V[i][h]
+ * where K/V[i][h] are the first context_lens[i] tokens reached through
+ * block_tables[i][token / block_size].
+ *
+ *   out            [num_seqs][num_heads][head_size]          T, contiguous
+ *   query          [num_seqs][num_heads][head_size]          T, row stride
+ *                  q_stride elements (query.stride(0)), inner dims contiguous
+ *   key_cache      layout above                              T
+ *   value_cache    layout above                              T
+ *   block_tables   [num_seqs][max_num_blocks_per_seq]        int32
+ *   context_lens   [num_seqs]                                int32
+ *   max_context_len upper bound of context_lens (sizes the split-context
+ *                  schedule only; the reference used it to size shared memory)
+ *
+ * head_size in {64, 80, 96, 128}, block_size in {8, 16, 32}, any pa_dtype --
+ * the reference's dispatch set (attention_kernels.cu:370-400, 416-448,
+ * 460-468); anything else returns the matching PA_ERR_UNSUPPORTED_* code
+ * (the reference raises through TORCH_CHECK).
+ *
+ * Differences from the reference kernel, all deliberate:
+ *   - 64-bit element offsets (num_blocks*num_heads*head_size*block_size may
+ *     exceed 2^31; the reference overflows there);
+ *   - tokens >= context_len in the last block are masked, never multiplied,
+ *     so non-finite garbage in unwritten cache slots cannot reach the output;
+ *   - no limit on context length from shared memory;
+ *   - context_len == 0 yields an all-zero output row.
+ * key_cache, value_cache, query rows and out must be 16-byte aligned.
+ */
+PA_API int pa_decode_attention(void* out, const void* query, const void* key_cache,
+                        const void* value_cache, float scale,
+                        const int32_t* block_tables,
+                        const int32_t* context_lens, int32_t num_seqs,
+                        int32_t num_heads, int32_t head_size,
+                        int32_t block_size, int32_t max_num_blocks_per_seq,
+                        int32_t max_context_len, int64_t q_stride,
+                        int32_t dtype, void* stream);
+
+/* Launch-shape overrides for tuning and tests; 0 / negative = automatic. */
+typedef struct pa_decode_tuning {
+  int32_t variant;    /* 0 auto, 1 direct global loads, 2 bulk-copy staged  */
+  int32_t num_warps;  /* warps per CTA working on one (seq, head, split)     */
+  int32_t num_stages; /* pages in flight per warp (variant 2)                */
+  int32_t num_splits; /* context partitions per (seq, head)                  */
+} pa_decode_tuning;
+
+/* Same operator with explicit launch shape (tuning == NULL -> automatic). */
+PA_API int pa_decode_attention_ex(void* out, const void* query, const void* key_cache,
+                           const void* value_cache, float scale,
+                           const int32_t* block_tables,
+                           const int32_t* context_lens, int32_t num_seqs,
+                           int32_t num_heads, int32_t head_size,
+                           int32_t block_size, int32_t max_num_blocks_per_seq,
+                           int32_t max_context_len, int64_t q_stride,
+                           int32_t dtype, const pa_decode_tuning* tuning,
+                           void* stream);
+
+/* The launch shape pa_decode_attention would pick for these sizes. */
+PA_API int pa_decode_attention_plan(int32_t num_seqs, int32_t num_heads,
+                             int32_t head_size, int32_t block_size,
+                             int32_t max_context_len, int32_t dtype,
+                             pa_decode_tuning* plan_out);
+
+/* ------------------------------------------------------------------------ */
+/* KV-cache movers (bit-exact)                                              */
+/* ------------------------------------------------------------------------ */
+
+/*
+ * replaces: cache_ops.reshape_and_cache
+ *           csrc/cache.cpp:17-22, csrc/cache_kernels.cu:186-224 (kernel :142-182)
+ *
+ * Scatters the new tokens' key/value rows into the paged caches:
+ *   slot = slot_mapping[t]; blk = slot / block_size; off = slot % block_size
+ *   key_cache  [blk][h][d / x][off][d % x] = key  [t][h][d]
+ *   value_cache[blk][h][d][off]            = value[t][h][d]
+ * key/value are [num_tokens][num_heads][head_size] with row strides
+ * key_stride / value_stride (elements).  A negative slot skips the token
+ * (the reference has no such case and would write out of bounds).
+ */
+PA_API int pa_reshape_and_cache(const void* key, const void* value, void* key_cache,
+                         void* value_cache, const int32_t* slot_mapping,
+                         int32_t num_tokens, int32_t num_heads,
+                         int32_t head_size, int32_t block_size,
+                         int64_t key_stride, int64_t value_stride,
+                         int32_t dtype, void* stream);
+
+/*
+ * replaces: cache_ops.gather_cached_kv
+ *           csrc/cache.cpp:24-29, csrc/cache_kernels.cu:348-386 (kernels :229-344)
+ * Inverse of pa_reshape_and_cache: key/value rows <- cache at slot_mapping.
+ */
+PA_API int pa_gather_cached_kv(void* key, void* value, const void* key_cache,
+                        const void* value_cache, const int32_t* slot_mapping,
+                        int32_t num_tokens, int32_t num_heads,
+                        int32_t head_size, int32_t block_size,
+                        int64_t key_stride, int64_t value_stride,
+                        int32_t dtype, void* stream);
+
+/*
+ * replaces: cache_ops.copy_blocks
+ *           csrc/cache.cpp:11-15, csrc/cache_kernels.cu:82-138 (kernel :52-78)
+ *
+ * Copy-on-write: for every layer and every pair p, copies block
+ * pairs[2p] -> block pairs[2p+1] inside that layer's key cache and inside
+ * its value cache.  key_cache_ptrs / value_cache_ptrs are HOST arrays of
+ * num_layers device base pointers; pairs is a HOST array of 2*num_pairs
+ * block numbers; block_bytes = num_heads*head_size*block_size*sizeof(T).
+ * Tables travel as kernel parameters: no staging allocation, no host
+ * synchronisation (the reference does three blocking pageable H2D copies).
+ * As in the reference, a destination must not be another pair's source.
+ */
+PA_API int pa_copy_blocks(void* const* key_cache_ptrs, void* const* value_cache_ptrs,
+                   int32_t num_layers, const int64_t* pairs, int64_t num_pairs,
+                   int64_t block_bytes, void* stream);
+
+/*
+ * replaces: cache_ops.swap_blocks
+ *           csrc/cache.cpp:6-9, csrc/cache_kernels.cu:9-47
+ *
+ * dst[dst_blocks[i]] = src[src_blocks[i]] for i < num_blocks, whole blocks of
+ * block_bytes.  kind selects device/host sides; host memory may be pageable
+ * or pinned (pinned is what vllm/worker/cache_engine.py:88-97 allocates).
+ * Runs of consecutive (src, dst) block numbers are merged into one DMA.
+ * src_blocks / dst_blocks are HOST arrays.
+ */
+PA_API int pa_swap_blocks(const void* src, void* dst, int64_t block_bytes,
+                   const int64_t* src_blocks, const int64_t* dst_blocks,
+                   int64_t num_blocks, int32_t kind, void* stream);
+
+#ifdef __cplusplus
+} /* extern "C" */
+#endif
+
+#endif /* PAGED_ATTENTION_B200_H_ */

@@ -1,0 +1,120 @@
+"""Seeded input generators shared by make_golden.py (run where /root/reference
+exists) and the tests (run anywhere).  Inputs come from numpy's frozen
+RandomState streams, so they are identical on every machine; the golden files
+store a SHA-256 of the inputs next to the reference outputs to prove it.
+"""
+from __future__ import annotations
+
+import hashlib
+from typing import Dict, List
+
+import numpy as np
+import torch
+
+DTYPES = {"f16": torch.float16, "bf16": torch.bfloat16, "f32": torch.float32}
+HEAD_SIZES = (64, 80, 96, 128)
+BLOCK_SIZES = (8, 16, 32)
+
+
+def _tensor(rs: np.random.RandomState, shape, dtype: torch.dtype, dist: str) -> torch.Tensor:
+    if dist == "ref":      # the reference tests' distribution (test_attention.py:170,177,181)
+        a = rs.uniform(-1e-3, 1e-3, size=shape)
+    elif dist == "unit":   # unit-scale values: a non-vacuous check at the stated tolerance
+        a = rs.standard_normal(size=shape)
+    else:
+        raise ValueError(dist)
+    return torch.from_numpy(a.astype(np.float32)).to(dtype)
+
+
+def attention_case_ids() -> List[str]:
+    ids = []
+    for dt in DTYPES:
+        for b in BLOCK_SIZES:
+            for d in HEAD_SIZES:
+                ids.append(f"{dt}-b{b}-d{d}-ref")
+    # unit-scale inputs on the shapes the benchmarks use
+    for dt in DTYPES:
+        ids.append(f"{dt}-b16-d128-unit")
+        ids.append(f"{dt}-b8-d80-unit")
+        ids.append(f"{dt}-b32-d96-unit")
+    return ids
+
+
+def attention_case(case_id: str) -> Dict[str, object]:
+    """Small decode-attention problem: 5 sequences, 3 heads, 24 blocks, context <= 180,
+    block tables with repeated blocks, query sliced out of a fused qkv tensor."""
+    dt, b, d, dist = case_id.split("-")
+    dtype, block_size, head_size = DTYPES[dt], int(b[1:]), int(d[1:])
+    seed = int(hashlib.sha256(case_id.encode()).hexdigest()[:8], 16)
+    rs = np.random.RandomState(seed)
+    num_seqs, num_heads, num_blocks, max_ctx = 5, 3, 24, 180
+    x = 16 // torch.empty((), dtype=dtype).element_size()
+    qkv = _tensor(rs, (num_seqs, 3, num_heads, head_size), dtype, dist)
+    query = qkv[:, 0]                                      # row stride 3*H*D, as in the reference test (:168-171)
+    key_cache = _tensor(rs, (num_blocks, num_heads, head_size // x, block_size, x), dtype, dist)
+    value_cache = _tensor(rs, (num_blocks, num_heads, head_size, block_size), dtype, dist)
+    ctx = [int(v) for v in rs.randint(1, max_ctx + 1, size=num_seqs)]
+    ctx[0] = block_size * 3            # ends exactly on a block boundary
+    ctx[1] = 1                         # single token
+    max_blocks = (max(ctx) + block_size - 1) // block_size + 2     # rows longer than needed (zero padded)
+    tables = np.zeros((num_seqs, max_blocks), dtype=np.int32)
+    for i, c in enumerate(ctx):
+        n = (c + block_size - 1) // block_size
+        tables[i, :n] = rs.randint(0, num_blocks, size=n)
+    return {
+        "dtype": dtype, "block_size": block_size, "head_size": head_size, "num_heads": num_heads,
+        "scale": float(1.0 / (head_size ** 0.5)),
+        "query": query, "key_cache": key_cache, "value_cache": value_cache,
+        "block_tables": torch.from_numpy(tables), "context_lens": torch.tensor(ctx, dtype=torch.int32),
+        "max_context_len": max(ctx),
+    }
+
+
+def cache_case_ids() -> List[str]:
+    return [f"{dt}-b{b}-d{d}" for dt in DTYPES for (b, d) in ((8, 16), (16, 64), (32, 128), (16, 80))]
+
+
+def cache_case(case_id: str) -> Dict[str, object]:
+    """Inputs for reshape_and_cache / gather_cached_kv / copy_blocks / swap_blocks."""
+    dt, b, d = case_id.split("-")
+    dtype, block_size, head_size = DTYPES[dt], int(b[1:]), int(d[1:])
+    seed = int(hashlib.sha256(("cache" + case_id).encode()).hexdigest()[:8], 16)
+    rs = np.random.RandomState(seed)
+    num_tokens, num_heads, num_blocks, num_layers = 7, 3, 10, 3
+    x = 16 // torch.empty((), dtype=dtype).element_size()
+    qkv = _tensor(rs, (num_tokens, 3, num_heads, head_size), dtype, "unit")
+    slots = rs.choice(num_blocks * block_size, size=num_tokens, replace=False).astype(np.int32)
+    kshape = (num_blocks, num_heads, head_size // x, block_size, x)
+    vshape = (num_blocks, num_heads, head_size, block_size)
+    key_caches = [_tensor(rs, kshape, dtype, "unit") for _ in range(num_layers)]
+    value_caches = [_tensor(rs, vshape, dtype, "unit") for _ in range(num_layers)]
+    perm = rs.permutation(num_blocks)
+    srcs, dsts = perm[:3], perm[3:8]
+    copy_map = {int(srcs[0]): [int(dsts[0])], int(srcs[1]): [int(dsts[1]), int(dsts[2])], int(srcs[2]): [int(dsts[3])]}
+    swap_map = {int(s): int(t) for s, t in zip(rs.permutation(num_blocks)[:4], rs.permutation(num_blocks)[:4])}
+    return {
+        "dtype": dtype, "block_size": block_size, "head_size": head_size, "num_heads": num_heads,
+        "key": qkv[:, 1], "value": qkv[:, 2], "slot_mapping": torch.from_numpy(slots),
+        "key_caches": key_caches, "value_caches": value_caches, "copy_map": copy_map, "swap_map": swap_map,
+    }
+
+
+def to_numpy(t: torch.Tensor) -> np.ndarray:
+    """Bit pattern of a tensor as a numpy array (bf16/f16 -> uint16)."""
+    t = t.contiguous()
+    if t.dtype in (torch.float16, torch.bfloat16):
+        return t.view(torch.int16).numpy().view(np.uint16).copy()
+    return t.numpy().copy()
+
+
+def from_numpy(a: np.ndarray, dtype: torch.dtype) -> torch.Tensor:
+    if dtype in (torch.float16, torch.bfloat16):
+        return torch.from_numpy(a.view(np.int16).copy()).view(dtype)
+    return torch.from_numpy(a.copy())
+
+
+def digest(*tensors: torch.Tensor) -> str:
+    h = hashlib.sha256()
+    for t in tensors:
+        h.update(to_numpy(t).tobytes())
+    return h.hexdigest()

@@ -1,0 +1,86 @@
+"""ctypes binding of libpaged_b200.so (the C ABI in include/paged_attention_b200.h).
+
+There is no fallback: if the library is missing, `lib()` raises, and every
+operator in attention_ops / cache_ops fails loudly.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import threading
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "lib", "libpaged_b200.so")
+
+PA_F16, PA_BF16, PA_F32 = 0, 1, 2
+PA_COPY_D2D, PA_COPY_D2H, PA_COPY_H2D = 0, 1, 2
+
+PA_OK = 0
+PA_ERR_UNSUPPORTED_HEAD_SIZE = -1
+PA_ERR_UNSUPPORTED_BLOCK_SIZE = -2
+PA_ERR_UNSUPPORTED_DTYPE = -3
+PA_ERR_INVALID_ARGUMENT = -4
+PA_ERR_CUDA = -5
+
+
+class DecodeTuning(C.Structure):
+    """Mirror of `pa_decode_tuning`."""
+    _fields_ = [("variant", C.c_int32), ("num_warps", C.c_int32),
+                ("num_stages", C.c_int32), ("num_splits", C.c_int32)]
+
+
+_vp, _i32, _i64, _f32 = C.c_void_p, C.c_int32, C.c_int64, C.c_float
+
+# name -> (restype, argtypes); must list every PA_API symbol of the header
+SIGNATURES = {
+    "pa_abi_version": (C.c_int, []),
+    "pa_last_error": (C.c_char_p, []),
+    "pa_compiled_sm": (C.c_int, []),
+    "pa_launch_count": (C.c_uint64, []),
+    "pa_release_workspaces": (C.c_int, []),
+    "pa_decode_attention": (C.c_int, [_vp, _vp, _vp, _vp, _f32, _vp, _vp, _i32, _i32, _i32, _i32, _i32, _i32,
+                                      _i64, _i32, _vp]),
+    "pa_decode_attention_ex": (C.c_int, [_vp, _vp, _vp, _vp, _f32, _vp, _vp, _i32, _i32, _i32, _i32, _i32, _i32,
+                                         _i64, _i32, C.POINTER(DecodeTuning), _vp]),
+    "pa_decode_attention_plan": (C.c_int, [_i32, _i32, _i32, _i32, _i32, _i32, C.POINTER(DecodeTuning)]),
+    "pa_reshape_and_cache": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _i64, _i64, _i32, _vp]),
+    "pa_gather_cached_kv": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _i64, _i64, _i32, _vp]),
+    "pa_copy_blocks": (C.c_int, [C.POINTER(_vp), C.POINTER(_vp), _i32, C.POINTER(_i64), _i64, _i64, _vp]),
+    "pa_swap_blocks": (C.c_int, [_vp, _vp, _i64, C.POINTER(_i64), C.POINTER(_i64), _i64, _i32, _vp]),
+}
+
+_lib = None
+_lock = threading.Lock()
+
+
+def lib() -> C.CDLL:
+    """Loads the shared library once; raises RuntimeError if it has not been built."""
+    global _lib
+    if _lib is None:
+        with _lock:
+            if _lib is None:
+                if not os.path.exists(LIB_PATH):
+                    raise RuntimeError(
+                        f"{LIB_PATH} is missing: build it with `python vllm-v0.1.0_b200/build.py` "
+                        "(there is no CPU or PyTorch fallback for these operators)")
+                handle = C.CDLL(LIB_PATH)
+                for name, (res, args) in SIGNATURES.items():
+                    fn = getattr(handle, name)
+                    fn.restype = res
+                    fn.argtypes = args
+                _lib = handle
+    return _lib
+
+
+def last_error() -> str:
+    return lib().pa_last_error().decode("utf-8", "replace")
+
+
+def check(rc: int) -> None:
+    """Maps a non-zero status to RuntimeError, as TORCH_CHECK does in the reference."""
+    if rc != PA_OK:
+        raise RuntimeError(f"libpaged_b200: {last_error()} (status {rc})")
+
+
+def launch_count() -> int:
+    return int(lib().pa_launch_count())

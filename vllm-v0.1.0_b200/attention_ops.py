@@ -1,0 +1,95 @@
+"""Drop-in for the reference's `vllm.attention_ops` extension module.
+
+Reference interface: csrc/attention.cpp:3-19 (pybind11) and
+csrc/attention/attention_kernels.cu:450-469 (host entry); call site
+vllm/model_executor/layers/attention.py:81-91.  Same name, positional
+arguments and in-place semantics; errors surface as RuntimeError.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional
+
+import torch
+
+from . import _cabi
+
+_DTYPES = {torch.float16: _cabi.PA_F16, torch.bfloat16: _cabi.PA_BF16, torch.float32: _cabi.PA_F32}
+
+
+def _dtype_code(t: torch.Tensor) -> int:
+    try:
+        return _DTYPES[t.dtype]
+    except KeyError:
+        raise RuntimeError(f"Unsupported data type: {t.dtype}") from None
+
+
+def _require_cuda(name: str, t: torch.Tensor, device: torch.device) -> None:
+    if not t.is_cuda:
+        raise RuntimeError(f"{name} must be a CUDA tensor (there is no CPU path)")
+    if t.device != device:
+        raise RuntimeError(f"{name} is on {t.device}, expected {device}")
+
+
+def single_query_cached_kv_attention(
+    out: torch.Tensor,            # [num_seqs, num_heads, head_size]
+    query: torch.Tensor,          # [num_seqs, num_heads, head_size], row-strided
+    key_cache: torch.Tensor,      # [num_blocks, num_heads, head_size/x, block_size, x]
+    value_cache: torch.Tensor,    # [num_blocks, num_heads, head_size, block_size]
+    scale: float,
+    block_tables: torch.Tensor,   # [num_seqs, max_num_blocks_per_seq] int32
+    context_lens: torch.Tensor,   # [num_seqs] int32
+    block_size: int,
+    max_context_len: int,
+    *,
+    tuning: Optional[_cabi.DecodeTuning] = None,
+) -> None:
+    """out[i, h] = softmax(scale * q[i, h] . K^T) . V over the first context_lens[i]
+    cached tokens of sequence i, reached through block_tables[i].
+
+    `tuning` (keyword-only, not part of the reference signature) forces a launch
+    shape; tests and the tuning sweep use it.
+    """
+    dev = query.device
+    for name, t in (("out", out), ("query", query), ("key_cache", key_cache), ("value_cache", value_cache),
+                    ("block_tables", block_tables), ("context_lens", context_lens)):
+        _require_cuda(name, t, dev)
+    code = _dtype_code(query)
+    if out.dtype != query.dtype or key_cache.dtype != query.dtype or value_cache.dtype != query.dtype:
+        raise RuntimeError("out, query, key_cache and value_cache must share one dtype")
+    if block_tables.dtype != torch.int32 or context_lens.dtype != torch.int32:
+        # the reference's data_ptr<int>() throws on anything else (attention_kernels.cu:358-359)
+        raise RuntimeError("block_tables and context_lens must be int32")
+    if query.dim() != 3 or out.dim() != 3 or key_cache.dim() != 5 or value_cache.dim() != 4 or block_tables.dim() != 2:
+        raise RuntimeError("unexpected tensor rank")
+    num_seqs, num_heads, head_size = query.shape
+    if tuple(out.shape) != (num_seqs, num_heads, head_size) or not out.is_contiguous():
+        raise RuntimeError("out must be a contiguous [num_seqs, num_heads, head_size] tensor")
+    if query.stride(2) != 1 or query.stride(1) != head_size:
+        raise RuntimeError("query must be contiguous in its last two dimensions")
+    if not key_cache.is_contiguous() or not value_cache.is_contiguous() or not block_tables.is_contiguous() \
+            or not context_lens.is_contiguous():
+        raise RuntimeError("caches, block_tables and context_lens must be contiguous")
+    if value_cache.shape[1] != num_heads or value_cache.shape[2] != head_size or value_cache.shape[3] != block_size:
+        raise RuntimeError("value_cache shape does not match [num_blocks, num_heads, head_size, block_size]")
+    if block_tables.shape[0] != num_seqs or context_lens.numel() != num_seqs:
+        raise RuntimeError("block_tables / context_lens row count does not match query")
+
+    lib = _cabi.lib()
+    stream = torch.cuda.current_stream(dev).cuda_stream
+    with torch.cuda.device(dev):
+        rc = lib.pa_decode_attention_ex(
+            out.data_ptr(), query.data_ptr(), key_cache.data_ptr(), value_cache.data_ptr(), float(scale),
+            block_tables.data_ptr(), context_lens.data_ptr(), num_seqs, num_heads, head_size, int(block_size),
+            block_tables.shape[1], int(max_context_len), query.stride(0), code,
+            C.byref(tuning) if tuning is not None else None, stream)
+    _cabi.check(rc)
+
+
+def decode_plan(num_seqs: int, num_heads: int, head_size: int, block_size: int, max_context_len: int,
+                dtype: torch.dtype) -> _cabi.DecodeTuning:
+    """The launch shape the library picks for these sizes (needs no GPU)."""
+    plan = _cabi.DecodeTuning(0, 0, 0, 0)
+    _cabi.check(_cabi.lib().pa_decode_attention_plan(num_seqs, num_heads, head_size, block_size, max_context_len,
+                                                     _DTYPES[dtype], C.byref(plan)))
+    return plan

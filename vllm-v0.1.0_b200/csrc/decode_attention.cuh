@@ -1,0 +1,545 @@
+// Paged decode attention for sm_100a.
+//
+// Replaces the reference kernel single_query_cached_kv_attention_kernel
+// (csrc/attention/attention_kernels.cu:67-314 of the reference) behind the
+// same operator contract; the design is not derived from it:
+//
+//   * one CTA per (head, sequence, context split); its W warps take whole
+//     pages round-robin and never synchronise with each other until the end;
+//   * every warp runs a single-pass (online) softmax over its pages, so no
+//     logits row lives in shared memory and context length is unbounded;
+//   * pages -- the contiguous D*B*sizeof(T) bytes of one (block, head) in the
+//     key cache and in the value cache -- are fetched by the TMA engine with
+//     cp.async.bulk into a per-warp ring of stages, completion signalled on an
+//     mbarrier; the block-table row is staged in shared memory first so the
+//     indirection never sits on the critical path;
+//   * 16-bit types never go through a convert: products use the sm_100a
+//     mixed-precision FMA (FHFMA: fp16/bf16 operands, exact product, fp32
+//     accumulate); the warp max is one CREDUX.MAX.F32;
+//   * tokens past context_len are masked by selection, never by multiplying,
+//     so garbage (NaN/Inf) in unwritten slots of the last block is harmless;
+//   * every offset is 64-bit.
+//
+// A second load path (PageSrc = GmemPage) reads pages straight from global
+// memory with streaming 16-byte loads; it shares all of the arithmetic.
+#pragma once
+
+#include <math_constants.h>
+
+#include "pa_common.cuh"
+
+namespace pa {
+
+// ---------------------------------------------------------------------------
+// compile-time geometry of one (T, head_size D, block_size B) combination
+// ---------------------------------------------------------------------------
+template <typename T, int D, int B>
+struct Geom {
+  static constexpr int kS = T::kSize;
+  static constexpr int kX = 16 / kS;                   // elements per 16-byte vector
+  // key page  [D/X][B] vectors: vector (c, t) = elements c*X..c*X+X-1 of token t
+  static constexpr int kNch = D / kX;                  // chunks per token
+  static constexpr int kTl = B < 16 ? B : 16;          // lanes along tokens
+  static constexpr int kG = kWarp / kTl;               // lane groups along chunks
+  static constexpr int kTpl = B / kTl;                 // tokens per lane
+  static constexpr int kCpl = (kNch + kG - 1) / kG;    // chunks per lane
+  static constexpr bool kKExact = (kNch % kG) == 0;
+  // value page [D][B/X] vectors: vector (d, tb) = tokens tb*X..tb*X+X-1 of row d
+  static constexpr int kVpr = B / kX;                  // vectors per row
+  static constexpr int kRpi = kWarp / kVpr;            // rows per warp iteration
+  static constexpr int kNvi = (D + kRpi - 1) / kRpi;   // iterations = accumulators per lane
+  static constexpr bool kVExact = (D % kRpi) == 0;
+  static constexpr int kPageBytes = D * B * kS;
+  static constexpr int kPbufBytes = B * kS;            // one page of probabilities
+  static_assert(D % kX == 0, "head_size must be a multiple of 16 bytes");
+  static_assert(B % kX == 0, "block_size must be a multiple of 16 bytes");
+};
+
+// page handles ---------------------------------------------------------------
+struct SmemPage {
+  uint32_t addr;
+  __device__ __forceinline__ uint4 ld(int vec) const {
+    uint4 r;
+    asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];"
+                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+                 : "r"(addr + static_cast<uint32_t>(vec) * 16u));
+    return r;
+  }
+};
+struct GmemPage {
+  const uint4* ptr;
+  __device__ __forceinline__ uint4 ld(int vec) const { return ldg_stream(ptr + vec); }
+};
+
+// 16-byte dot product step ----------------------------------------------------
+template <typename T>
+__device__ __forceinline__ void dot16(const uint4& a, const uint4& b, float& lo, float& hi) {
+  lo = mixfma_lo<T>(a.x, b.x, lo);
+  hi = mixfma_hi<T>(a.x, b.x, hi);
+  lo = mixfma_lo<T>(a.y, b.y, lo);
+  hi = mixfma_hi<T>(a.y, b.y, hi);
+  lo = mixfma_lo<T>(a.z, b.z, lo);
+  hi = mixfma_hi<T>(a.z, b.z, hi);
+  lo = mixfma_lo<T>(a.w, b.w, lo);
+  hi = mixfma_hi<T>(a.w, b.w, hi);
+}
+template <>
+__device__ __forceinline__ void dot16<F32>(const uint4& a, const uint4& b, float& lo, float& hi) {
+  lo = fmaf(__uint_as_float(a.x), __uint_as_float(b.x), lo);
+  hi = fmaf(__uint_as_float(a.y), __uint_as_float(b.y), hi);
+  lo = fmaf(__uint_as_float(a.z), __uint_as_float(b.z), lo);
+  hi = fmaf(__uint_as_float(a.w), __uint_as_float(b.w), hi);
+}
+
+__device__ __forceinline__ float fast_exp2(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
+// Probabilities are kept relative to the running maximum (<= 1).  For fp16 they
+// are stored scaled by 2^14 so that the 16-bit copy used in the P.V products
+// keeps tokens down to 2^-38 of the maximum; the row sum carries the same
+// factor, so it cancels in the final division.
+template <typename T> struct ProbScale { static constexpr float kLog2 = 0.f; };
+template <> struct ProbScale<F16> { static constexpr float kLog2 = 14.f; };
+
+// running state of one warp ----------------------------------------------------
+template <typename T, int D, int B>
+struct WarpState {
+  using Gm = Geom<T, D, B>;
+  float m;              // running maximum of scaled logits (log2 domain)
+  float l;              // this lane's share of the running sum of probabilities
+  float acc[Gm::kNvi];  // this lane's rows of the running P.V
+};
+
+// One page: logits for its B tokens, online-softmax update, P.V accumulate.
+// nvalid = number of tokens of this page inside the context (B unless last).
+template <typename T, int D, int B, typename Page>
+__device__ __forceinline__ void process_page(const Page& kp, const Page& vp,
+                                             const uint4 (&q)[Geom<T, D, B>::kCpl],
+                                             WarpState<T, D, B>& st, float scale_log2,
+                                             int nvalid, uint32_t pbuf, int lane) {
+  using Gm = Geom<T, D, B>;
+  const int tl = lane % Gm::kTl;
+  const int g = lane / Gm::kTl;
+
+  // ---- q . k -------------------------------------------------------------
+  float lo[Gm::kTpl], hi[Gm::kTpl];
+#pragma unroll
+  for (int tt = 0; tt < Gm::kTpl; ++tt) { lo[tt] = 0.f; hi[tt] = 0.f; }
+#pragma unroll
+  for (int cc = 0; cc < Gm::kCpl; ++cc) {
+    const int c = cc * Gm::kG + g;
+    if (Gm::kKExact || c < Gm::kNch) {
+#pragma unroll
+      for (int tt = 0; tt < Gm::kTpl; ++tt) {
+        const uint4 kv = kp.ld(c * B + tt * Gm::kTl + tl);
+        dot16<T>(q[cc], kv, lo[tt], hi[tt]);
+      }
+    }
+  }
+  float s[Gm::kTpl];
+  float pm = -CUDART_INF_F;
+#pragma unroll
+  for (int tt = 0; tt < Gm::kTpl; ++tt) {
+    float v = lo[tt] + hi[tt];
+#pragma unroll
+    for (int o = Gm::kTl; o < kWarp; o <<= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    v *= scale_log2;
+    // masked tokens are replaced, not multiplied: their logit may be NaN/Inf
+    if (tt * Gm::kTl + tl >= nvalid) v = -CUDART_INF_F;
+    s[tt] = v;
+    pm = fmaxf(pm, v);
+  }
+
+  // ---- online softmax -----------------------------------------------------
+  pm = warp_max(pm);
+  if (pm > st.m) {  // warp-uniform
+    const float alpha = fast_exp2(st.m - pm);
+    st.m = pm;
+    st.l *= alpha;
+#pragma unroll
+    for (int i = 0; i < Gm::kNvi; ++i) st.acc[i] *= alpha;
+  }
+  const float off = ProbScale<T>::kLog2 - st.m;
+#pragma unroll
+  for (int tt = 0; tt < Gm::kTpl; ++tt) {
+    const float p = fast_exp2(s[tt] + off);  // exp2(-inf) == 0 for masked tokens
+    const int t = tt * Gm::kTl + tl;
+    if constexpr (T::kSize == 2) {
+      const uint32_t pk = pack2<T>(p, 0.f);
+      if (g == 0) {
+        st.l += unpack_lo<T>(pk);  // sum what the products will actually use
+        asm volatile("st.shared.u16 [%0], %1;"
+                     :: "r"(pbuf + t * 2), "h"(static_cast<uint16_t>(pk)) : "memory");
+      }
+    } else {
+      if (g == 0) {
+        st.l += p;
+        asm volatile("st.shared.f32 [%0], %1;" :: "r"(pbuf + t * 4), "f"(p) : "memory");
+      }
+    }
+  }
+  __syncwarp();
+
+  // ---- p . v --------------------------------------------------------------
+  const int tb = lane % Gm::kVpr;
+  uint4 pv;
+  asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];"
+               : "=r"(pv.x), "=r"(pv.y), "=r"(pv.z), "=r"(pv.w)
+               : "r"(pbuf + tb * 16) : "memory");
+  if (nvalid >= B) {
+#pragma unroll
+    for (int i = 0; i < Gm::kNvi; ++i) {
+      if (Gm::kVExact || i * Gm::kRpi + lane / Gm::kVpr < D) {
+        const uint4 vv = vp.ld(i * kWarp + lane);
+        float hi2 = 0.f;
+        dot16<T>(pv, vv, st.acc[i], hi2);
+        st.acc[i] += hi2;
+      }
+    }
+  } else {
+    // last block of the context: zero the value elements of masked tokens
+    uint32_t msk[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      if constexpr (T::kSize == 2) {
+        const int t0 = tb * 8 + 2 * j;
+        msk[j] = (t0 < nvalid ? 0x0000ffffu : 0u) | (t0 + 1 < nvalid ? 0xffff0000u : 0u);
+      } else {
+        msk[j] = (tb * 4 + j < nvalid) ? 0xffffffffu : 0u;
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < Gm::kNvi; ++i) {
+      if (Gm::kVExact || i * Gm::kRpi + lane / Gm::kVpr < D) {
+        uint4 vv = vp.ld(i * kWarp + lane);
+        vv.x &= msk[0]; vv.y &= msk[1]; vv.z &= msk[2]; vv.w &= msk[3];
+        float hi2 = 0.f;
+        dot16<T>(pv, vv, st.acc[i], hi2);
+        st.acc[i] += hi2;
+      }
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------
+// kernel
+// ---------------------------------------------------------------------------
+struct DecodeParams {
+  void* out;                  // [S][H][D] T
+  const void* q;              // [S][H][D] T, row stride q_stride elements
+  const void* k_cache;
+  const void* v_cache;
+  const int32_t* block_tables;  // [S][MB]
+  const int32_t* context_lens;  // [S]
+  float* ws_part;             // [S][H][nsplit][D + 2]   (nsplit > 1)
+  uint32_t* ws_ticket;        // [S][H], zero between calls (nsplit > 1)
+  int64_t q_stride;
+  float scale_log2;           // scale * log2(e)
+  int32_t num_heads;
+  int32_t max_blocks_per_seq;
+  int32_t pages_per_split;
+  int32_t num_splits;
+  int32_t num_stages;
+  int32_t q_vec_ok;           // q rows are 16-byte aligned
+};
+
+// dynamic shared memory map (bytes), W = warps per CTA:
+//   [0, tbl_bytes)                       int32 block numbers of this split
+//   + W * (D + 2) floats                 end-of-CTA merge area
+//   + W * 2 * kPbufBytes(aligned 16)     probability pages (double-buffered)
+//   + W * S * 8                          mbarriers            (staged only)
+//   + W * S * 2 * kPageBytes             stage ring, 128-byte aligned (staged only)
+template <typename T, int D, int B>
+struct SmemMap {
+  using Gm = Geom<T, D, B>;
+  static constexpr int kPbufStride = ((2 * Gm::kPbufBytes + 15) / 16) * 16;
+  int tbl, red, pbuf, bars, ring, total;
+  __host__ __device__ SmemMap(int pages_per_split, int warps, int stages, bool staged) {
+    int o = 0;
+    tbl = o;  o += ((pages_per_split * 4 + 15) / 16) * 16;
+    red = o;  o += warps * (D + 2) * 4;  o = ((o + 15) / 16) * 16;
+    pbuf = o; o += warps * kPbufStride;
+    bars = o; o += staged ? warps * stages * 8 : 0;
+    o = ((o + 127) / 128) * 128;
+    ring = o; o += staged ? warps * stages * 2 * Gm::kPageBytes : 0;
+    total = o;
+  }
+};
+
+template <typename T, int D, int B, bool kStaged>
+__global__ void __launch_bounds__(256)
+paged_decode_kernel(const DecodeParams p) {
+  using Gm = Geom<T, D, B>;
+  extern __shared__ __align__(128) unsigned char smem[];
+
+  const int head = blockIdx.x;
+  const int seq = blockIdx.y;
+  const int split = blockIdx.z;
+  const int warp = threadIdx.x / kWarp;
+  const int lane = threadIdx.x % kWarp;
+  const int nwarps = blockDim.x / kWarp;
+  const int H = p.num_heads;
+
+  const SmemMap<T, D, B> map(p.pages_per_split, nwarps, p.num_stages, kStaged);
+  int32_t* tbl = reinterpret_cast<int32_t*>(smem + map.tbl);
+  float* red = reinterpret_cast<float*>(smem + map.red);
+
+  const int ctx = p.context_lens[seq];
+  const int first_page = split * p.pages_per_split;
+  // never walk past the block-table row or the split schedule, whatever context_lens says
+  const int pages_true = ctx > 0 ? (ctx + B - 1) / B : 0;
+  const int pages_cap = min(p.max_blocks_per_seq, p.pages_per_split * p.num_splits);
+  const int total_pages = min(pages_true, pages_cap);
+  int npages = total_pages - first_page;
+  npages = npages < 0 ? 0 : (npages > p.pages_per_split ? p.pages_per_split : npages);
+
+  if (p.num_splits == 1 && npages == 0) {
+    // empty context: the reference leaves an all-zero row (attention_kernels.cu:142,213)
+    for (int d = threadIdx.x; d < D; d += blockDim.x) {
+      const int64_t o = (static_cast<int64_t>(seq) * H + head) * D + d;
+      if constexpr (T::kSize == 2) reinterpret_cast<uint16_t*>(p.out)[o] = 0;
+      else reinterpret_cast<float*>(p.out)[o] = 0.f;
+    }
+    return;
+  }
+
+  // ---- stage the block-table slice; init barriers ---------------------------
+  {
+    const int32_t* row = p.block_tables + static_cast<int64_t>(seq) * p.max_blocks_per_seq + first_page;
+    for (int i = threadIdx.x; i < npages; i += blockDim.x) tbl[i] = row[i];
+  }
+  const uint32_t bars = smem_addr(smem + map.bars) + warp * p.num_stages * 8;
+  const uint32_t ring = smem_addr(smem + map.ring) + warp * p.num_stages * 2 * Gm::kPageBytes;
+  if constexpr (kStaged) {
+    if (lane == 0) {
+      for (int s = 0; s < p.num_stages; ++s) mbar_init(bars + s * 8, 1);
+      mbar_init_fence();
+    }
+  }
+
+  // ---- q row -> registers ------------------------------------------------------
+  uint4 q[Gm::kCpl];
+  {
+    const int g = lane / Gm::kTl;
+    const char* qrow = reinterpret_cast<const char*>(p.q) +
+                       (static_cast<int64_t>(seq) * p.q_stride + static_cast<int64_t>(head) * D) * T::kSize;
+#pragma unroll
+    for (int cc = 0; cc < Gm::kCpl; ++cc) {
+      const int c = cc * Gm::kG + g;
+      q[cc] = make_uint4(0u, 0u, 0u, 0u);
+      if (Gm::kKExact || c < Gm::kNch) {
+        if (p.q_vec_ok) {
+          q[cc] = *reinterpret_cast<const uint4*>(qrow + c * 16);
+        } else {
+          const uint16_t* h16 = reinterpret_cast<const uint16_t*>(qrow + c * 16);
+          uint32_t w[4];
+#pragma unroll
+          for (int j = 0; j < 4; ++j) w[j] = static_cast<uint32_t>(h16[2 * j]) | (static_cast<uint32_t>(h16[2 * j + 1]) << 16);
+          q[cc] = make_uint4(w[0], w[1], w[2], w[3]);
+        }
+      }
+    }
+  }
+  __syncthreads();  // tbl visible to every warp; barrier inits visible
+
+  WarpState<T, D, B> st;
+  st.m = -CUDART_INF_F;
+  st.l = 0.f;
+#pragma unroll
+  for (int i = 0; i < Gm::kNvi; ++i) st.acc[i] = 0.f;
+
+  // pages of this warp: local index warp + n * nwarps, n < n_my
+  const int n_my = npages > warp ? (npages - warp + nwarps - 1) / nwarps : 0;
+  const uint32_t pbuf0 = smem_addr(smem + map.pbuf) + warp * SmemMap<T, D, B>::kPbufStride;
+  const char* kbase = reinterpret_cast<const char*>(p.k_cache) + static_cast<int64_t>(head) * Gm::kPageBytes;
+  const char* vbase = reinterpret_cast<const char*>(p.v_cache) + static_cast<int64_t>(head) * Gm::kPageBytes;
+  const int64_t block_bytes = static_cast<int64_t>(H) * Gm::kPageBytes;
+  // local index of the context's last page and the number of tokens in it
+  const int last_local = pages_true <= pages_cap ? pages_true - 1 - first_page : -1;
+  const int tail = ctx - (pages_true - 1) * B;
+
+  if constexpr (kStaged) {
+    const int S = p.num_stages;
+    auto issue = [&](int n, int stage) {
+      const int64_t blk = tbl[warp + n * nwarps];
+      const uint32_t bar = bars + stage * 8;
+      const uint32_t dst = ring + stage * 2 * Gm::kPageBytes;
+      mbar_expect_tx(bar, 2 * Gm::kPageBytes);
+      bulk_g2s(dst, kbase + blk * block_bytes, Gm::kPageBytes, bar);
+      bulk_g2s(dst + Gm::kPageBytes, vbase + blk * block_bytes, Gm::kPageBytes, bar);
+    };
+    if (lane == 0) {
+      const int pre = n_my < S ? n_my : S;
+      for (int n = 0; n < pre; ++n) issue(n, n);
+    }
+    int stage = 0;
+    uint32_t parity = 0;
+    for (int n = 0; n < n_my; ++n) {
+      mbar_wait(bars + stage * 8, parity);
+      const int local = warp + n * nwarps;
+      const int nvalid = (local == last_local) ? tail : B;
+      const SmemPage kp{ring + stage * 2 * Gm::kPageBytes};
+      const SmemPage vp{kp.addr + Gm::kPageBytes};
+      process_page<T, D, B>(kp, vp, q, st, p.scale_log2, nvalid, pbuf0 + (n & 1) * Gm::kPbufBytes, lane);
+      __syncwarp();  // every lane is done reading this stage
+      if (lane == 0 && n + S < n_my) issue(n + S, stage);
+      if (++stage == S) { stage = 0; parity ^= 1u; }
+    }
+  } else {
+    for (int n = 0; n < n_my; ++n) {
+      const int local = warp + n * nwarps;
+      const int64_t blk = tbl[local];
+      const int nvalid = (local == last_local) ? tail : B;
+      const GmemPage kp{reinterpret_cast<const uint4*>(kbase + blk * block_bytes)};
+      const GmemPage vp{reinterpret_cast<const uint4*>(vbase + blk * block_bytes)};
+      process_page<T, D, B>(kp, vp, q, st, p.scale_log2, nvalid, pbuf0 + (n & 1) * Gm::kPbufBytes, lane);
+    }
+  }
+
+  // ---- merge the warps of this CTA ------------------------------------------------
+#pragma unroll
+  for (int i = 0; i < Gm::kNvi; ++i) {
+#pragma unroll
+    for (int o = 1; o < Gm::kVpr; o <<= 1) st.acc[i] += __shfl_xor_sync(0xffffffffu, st.acc[i], o);
+  }
+  st.l = warp_sum(st.l);
+  float* my = red + warp * (D + 2);
+  if (lane == 0) { my[D] = st.m; my[D + 1] = st.l; }
+  if (lane % Gm::kVpr == 0) {
+#pragma unroll
+    for (int i = 0; i < Gm::kNvi; ++i) {
+      const int d = i * Gm::kRpi + lane / Gm::kVpr;
+      if (Gm::kVExact || d < D) my[d] = st.acc[i];
+    }
+  }
+  __syncthreads();
+
+  const float eps = 1e-6f * exp2f(ProbScale<T>::kLog2);  // reference: 1/(sum + 1e-6), attention_kernels.cu:213
+  float cta_m = -CUDART_INF_F;
+  for (int w = 0; w < nwarps; ++w) cta_m = fmaxf(cta_m, red[w * (D + 2) + D]);
+  float cta_l = 0.f;
+  for (int w = 0; w < nwarps; ++w) {
+    const float mw = red[w * (D + 2) + D];
+    if (mw > -CUDART_INF_F) cta_l += red[w * (D + 2) + D + 1] * fast_exp2(mw - cta_m);
+  }
+
+  if (p.num_splits == 1) {
+    for (int d = threadIdx.x; d < D; d += blockDim.x) {
+      float a = 0.f;
+      for (int w = 0; w < nwarps; ++w) {
+        const float mw = red[w * (D + 2) + D];
+        if (mw > -CUDART_INF_F) a += red[w * (D + 2) + d] * fast_exp2(mw - cta_m);
+      }
+      const float r = a / (cta_l + eps);
+      const int64_t o = (static_cast<int64_t>(seq) * H + head) * D + d;
+      if constexpr (T::kSize == 2) reinterpret_cast<uint16_t*>(p.out)[o] = static_cast<uint16_t>(pack2<T>(r, 0.f));
+      else reinterpret_cast<float*>(p.out)[o] = r;
+    }
+    return;
+  }
+
+  // ---- split context: publish the partial, the last CTA to arrive combines -----
+  const int64_t item = static_cast<int64_t>(seq) * H + head;
+  float* part = p.ws_part + (item * p.num_splits + split) * (D + 2);
+  for (int d = threadIdx.x; d < D; d += blockDim.x) {
+    float a = 0.f;
+    for (int w = 0; w < nwarps; ++w) {
+      const float mw = red[w * (D + 2) + D];
+      if (mw > -CUDART_INF_F) a += red[w * (D + 2) + d] * fast_exp2(mw - cta_m);
+    }
+    __stcg(part + d, a);
+  }
+  if (threadIdx.x == 0) { __stcg(part + D, cta_m); __stcg(part + D + 1, cta_l); }
+  __threadfence();
+  __syncthreads();
+  __shared__ uint32_t s_last;
+  if (threadIdx.x == 0) {
+    const uint32_t prev = atomicAdd(p.ws_ticket + item, 1u);
+    s_last = (prev == static_cast<uint32_t>(p.num_splits) - 1u) ? 1u : 0u;
+    if (s_last) p.ws_ticket[item] = 0u;  // re-arm for the next call on this stream
+  }
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence();
+  const float* parts = p.ws_part + item * p.num_splits * (D + 2);
+  float gm = -CUDART_INF_F;
+  for (int s = 0; s < p.num_splits; ++s) gm = fmaxf(gm, __ldcg(parts + s * (D + 2) + D));
+  float gl = 0.f;
+  for (int s = 0; s < p.num_splits; ++s) {
+    const float ms = __ldcg(parts + s * (D + 2) + D);
+    if (ms > -CUDART_INF_F) gl += __ldcg(parts + s * (D + 2) + D + 1) * fast_exp2(ms - gm);
+  }
+  for (int d = threadIdx.x; d < D; d += blockDim.x) {
+    float a = 0.f;
+    for (int s = 0; s < p.num_splits; ++s) {
+      const float ms = __ldcg(parts + s * (D + 2) + D);
+      if (ms > -CUDART_INF_F) a += __ldcg(parts + s * (D + 2) + d) * fast_exp2(ms - gm);
+    }
+    const float r = a / (gl + eps);  // all splits empty (context_len == 0): 0 / eps == 0
+    const int64_t o = item * D + d;
+    if constexpr (T::kSize == 2) reinterpret_cast<uint16_t*>(p.out)[o] = static_cast<uint16_t>(pack2<T>(r, 0.f));
+    else reinterpret_cast<float*>(p.out)[o] = r;
+  }
+}
+
+// ---------------------------------------------------------------------------
+// host-side launch of one dtype (defined per dtype in decode_*.cu)
+// ---------------------------------------------------------------------------
+struct DecodeLaunch {
+  DecodeParams params;
+  int32_t num_seqs;
+  int32_t head_size;
+  int32_t block_size;
+  int32_t num_warps;
+  bool staged;
+  cudaStream_t stream;
+};
+
+// bytes of dynamic shared memory a launch needs (same formula as the kernel)
+int decode_smem_bytes(int dtype, int head_size, int block_size, int pages_per_split,
+                      int warps, int stages, bool staged);
+
+int launch_decode_f16(const DecodeLaunch& l);
+int launch_decode_bf16(const DecodeLaunch& l);
+int launch_decode_f32(const DecodeLaunch& l);
+
+#ifdef PA_DECODE_IMPL
+template <typename T, int D, int B, bool kStaged>
+static int launch_one(const DecodeLaunch& l) {
+  const SmemMap<T, D, B> map(l.params.pages_per_split, l.num_warps, l.params.num_stages, kStaged);
+  auto kern = paged_decode_kernel<T, D, B, kStaged>;
+  if (map.total > 48 * 1024) {
+    PA_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, map.total));
+  }
+  const dim3 grid(l.params.num_heads, l.num_seqs, l.params.num_splits);
+  kern<<<grid, l.num_warps * kWarp, map.total, l.stream>>>(l.params);
+  count_launch();
+  return check_cuda(cudaGetLastError(), "paged_decode_kernel launch");
+}
+
+template <typename T, int D>
+static int launch_block(const DecodeLaunch& l) {
+  switch (l.block_size) {
+    case 8:  return l.staged ? launch_one<T, D, 8, true>(l) : launch_one<T, D, 8, false>(l);
+    case 16: return l.staged ? launch_one<T, D, 16, true>(l) : launch_one<T, D, 16, false>(l);
+    case 32: return l.staged ? launch_one<T, D, 32, true>(l) : launch_one<T, D, 32, false>(l);
+    default: return set_error(PA_ERR_UNSUPPORTED_BLOCK_SIZE, "unsupported block size: %d", l.block_size);
+  }
+}
+
+template <typename T>
+static int launch_dtype(const DecodeLaunch& l) {
+  switch (l.head_size) {
+    case 64:  return launch_block<T, 64>(l);
+    case 80:  return launch_block<T, 80>(l);
+    case 96:  return launch_block<T, 96>(l);
+    case 128: return launch_block<T, 128>(l);
+    default:  return set_error(PA_ERR_UNSUPPORTED_HEAD_SIZE, "unsupported head size: %d", l.head_size);
+  }
+}
+#endif  // PA_DECODE_IMPL
+
+}  // namespace pa

@@ -1,0 +1,285 @@
+// Library plumbing and the decode-attention entry points of libpaged_b200:
+// error state, launch accounting, the split-context scratch buffers and the
+// launch-shape heuristic.  See include/paged_attention_b200.h for the ABI.
+#include <atomic>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <map>
+#include <mutex>
+#include <utility>
+
+#include "decode_attention.cuh"
+
+namespace pa {
+
+// ---------------------------------------------------------------------------
+// error state (thread-local) and launch counter
+// ---------------------------------------------------------------------------
+static thread_local char g_err[512] = "";
+static std::atomic<uint64_t> g_launches{0};
+
+int set_error(int code, const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+  return code;
+}
+
+int check_cuda(cudaError_t e, const char* what) {
+  if (e == cudaSuccess) return PA_OK;
+  return set_error(PA_ERR_CUDA, "CUDA error in %s: %s (%s)", what, cudaGetErrorName(e), cudaGetErrorString(e));
+}
+
+void count_launch(uint64_t n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
+
+// ---------------------------------------------------------------------------
+// per-(device, stream) scratch for split-context partials.
+// Layout: [tickets: items x uint32, padded to 256 B][partials: floats].
+// Tickets are zeroed when the buffer is created and re-armed by the kernel.
+// ---------------------------------------------------------------------------
+struct Workspace {
+  void* ptr = nullptr;
+  size_t bytes = 0;
+  size_t ticket_bytes = 0;
+};
+static std::mutex g_ws_mu;
+static std::map<std::pair<int, cudaStream_t>, Workspace> g_ws;
+
+static int get_workspace(cudaStream_t stream, size_t ticket_bytes, size_t part_bytes, uint32_t** tickets,
+                         float** parts) {
+  int dev = 0;
+  PA_CUDA_TRY(cudaGetDevice(&dev));
+  std::lock_guard<std::mutex> lock(g_ws_mu);
+  Workspace& w = g_ws[std::make_pair(dev, stream)];
+  ticket_bytes = (ticket_bytes + 255) / 256 * 256;
+  const size_t need = ticket_bytes + part_bytes;
+  if (w.bytes < need || w.ticket_bytes < ticket_bytes || w.bytes - w.ticket_bytes < part_bytes) {
+    if (w.ptr) {
+      PA_CUDA_TRY(cudaStreamSynchronize(stream));
+      PA_CUDA_TRY(cudaFree(w.ptr));
+      w = Workspace();
+    }
+    const size_t tb = ticket_bytes * 2;            // head-room: item count may grow
+    const size_t total = tb + (need - ticket_bytes) * 2;
+    PA_CUDA_TRY(cudaMalloc(&w.ptr, total));
+    w.bytes = total;
+    w.ticket_bytes = tb;
+    PA_CUDA_TRY(cudaMemsetAsync(w.ptr, 0, tb, stream));
+  }
+  *tickets = static_cast<uint32_t*>(w.ptr);
+  *parts = reinterpret_cast<float*>(static_cast<char*>(w.ptr) + w.ticket_bytes);
+  return PA_OK;
+}
+
+// ---------------------------------------------------------------------------
+// launch-shape heuristic
+// ---------------------------------------------------------------------------
+static int sm_count() {
+  static int cached[64] = {0};
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
+  if (cached[dev] == 0) {
+    int n = 0;
+    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
+    cached[dev] = n;
+  }
+  return cached[dev];
+}
+
+int decode_smem_bytes(int dtype, int head_size, int block_size, int pages_per_split, int warps, int stages,
+                      bool staged) {
+  const int page = head_size * block_size * dtype_size(dtype);
+  const int pbuf = ((2 * block_size * dtype_size(dtype) + 15) / 16) * 16;
+  int o = ((pages_per_split * 4 + 15) / 16) * 16;
+  o += warps * (head_size + 2) * 4;
+  o = ((o + 15) / 16) * 16;
+  o += warps * pbuf;
+  o += staged ? warps * stages * 8 : 0;
+  o = ((o + 127) / 128) * 128;
+  o += staged ? warps * stages * 2 * page : 0;
+  return o;
+}
+
+constexpr int kMaxSmem = 227 * 1024;
+constexpr int kMaxPagesPerSplit = 8192;  // block-table slice kept in shared memory (32 KiB)
+
+// Fills the zero fields of `t`.  Returns pages_per_split through the pointer.
+static int make_plan(int num_seqs, int num_heads, int head_size, int block_size, int max_context_len,
+                     int dtype, pa_decode_tuning* t, int* pages_per_split) {
+  const int page = head_size * block_size * dtype_size(dtype);
+  const int stage = 2 * page;
+  const int max_pages = max_context_len > 0 ? (max_context_len + block_size - 1) / block_size : 1;
+
+  if (t->variant <= 0) t->variant = 2;
+  const bool staged = t->variant == 2;
+  if (t->num_warps <= 0) {
+    t->num_warps = 4;
+    while (staged && t->num_warps > 1 && t->num_warps * 2 * stage > 160 * 1024) t->num_warps >>= 1;
+  }
+  if (t->num_warps > 8) t->num_warps = 8;
+  if (t->num_stages <= 0) {
+    // ~64 KiB of ring per CTA: three CTAs per SM, >= 128 KiB of loads in flight per SM
+    int s = (64 * 1024) / (t->num_warps * stage);
+    t->num_stages = s < 2 ? 2 : (s > 8 ? 8 : s);
+  }
+  if (!staged) t->num_stages = 1;
+  if (t->num_stages > 32) t->num_stages = 32;
+
+  if (t->num_splits <= 0) {
+    const int smem1 = decode_smem_bytes(dtype, head_size, block_size, 64, t->num_warps, t->num_stages, staged);
+    int resident = kMaxSmem / (smem1 + 1024);
+    const int by_threads = 2048 / (t->num_warps * kWarp);
+    if (resident > by_threads) resident = by_threads;
+    if (resident < 1) resident = 1;
+    const int64_t items = static_cast<int64_t>(num_seqs) * num_heads;
+    const int64_t want = static_cast<int64_t>(sm_count()) * resident * 8;  // ~8 CTAs per resident slot
+    int64_t ns = items > 0 ? (want + items - 1) / items : 1;
+    const int64_t cap = max_pages / (4 * t->num_warps);  // keep >= 4 pages per warp
+    if (ns > cap) ns = cap;
+    if (ns < 1) ns = 1;
+    t->num_splits = static_cast<int>(ns);
+  }
+  if (t->num_splits > max_pages) t->num_splits = max_pages;
+  if (t->num_splits < 1) t->num_splits = 1;
+  // pages per split, a multiple of the warp count so warps stay balanced
+  int pps = (max_pages + t->num_splits - 1) / t->num_splits;
+  pps = (pps + t->num_warps - 1) / t->num_warps * t->num_warps;
+  if (pps > kMaxPagesPerSplit) pps = kMaxPagesPerSplit / t->num_warps * t->num_warps;
+  t->num_splits = (max_pages + pps - 1) / pps;
+  if (t->num_splits > 65535) return set_error(PA_ERR_INVALID_ARGUMENT, "context too long: %d splits", t->num_splits);
+  *pages_per_split = pps;
+
+  // shrink the ring until the CTA fits
+  while (staged && t->num_stages > 1 &&
+         decode_smem_bytes(dtype, head_size, block_size, pps, t->num_warps, t->num_stages, true) > kMaxSmem)
+    --t->num_stages;
+  if (decode_smem_bytes(dtype, head_size, block_size, pps, t->num_warps, t->num_stages, staged) > kMaxSmem)
+    return set_error(PA_ERR_INVALID_ARGUMENT, "launch shape does not fit shared memory (warps %d, stages %d)",
+                     t->num_warps, t->num_stages);
+  return PA_OK;
+}
+
+static int check_shape(int head_size, int block_size, int dtype) {
+  // the reference's dispatch set: attention_kernels.cu:370-400 (head), :416-448 (block), :460-468 (dtype)
+  if (dtype != PA_F16 && dtype != PA_BF16 && dtype != PA_F32)
+    return set_error(PA_ERR_UNSUPPORTED_DTYPE, "unsupported data type: %d", dtype);
+  if (head_size != 64 && head_size != 80 && head_size != 96 && head_size != 128)
+    return set_error(PA_ERR_UNSUPPORTED_HEAD_SIZE, "unsupported head size: %d", head_size);
+  if (block_size != 8 && block_size != 16 && block_size != 32)
+    return set_error(PA_ERR_UNSUPPORTED_BLOCK_SIZE, "unsupported block size: %d", block_size);
+  return PA_OK;
+}
+
+static int decode(void* out, const void* query, const void* key_cache, const void* value_cache, float scale,
+                  const int32_t* block_tables, const int32_t* context_lens, int32_t num_seqs,
+                  int32_t num_heads, int32_t head_size, int32_t block_size, int32_t max_num_blocks_per_seq,
+                  int32_t max_context_len, int64_t q_stride, int32_t dtype, const pa_decode_tuning* tuning,
+                  cudaStream_t stream) {
+  int rc = check_shape(head_size, block_size, dtype);
+  if (rc != PA_OK) return rc;
+  if (num_seqs < 0 || num_heads <= 0 || max_num_blocks_per_seq < 0 || max_context_len < 0)
+    return set_error(PA_ERR_INVALID_ARGUMENT, "bad sizes (seqs %d, heads %d, max blocks %d, max context %d)",
+                     num_seqs, num_heads, max_num_blocks_per_seq, max_context_len);
+  if (num_seqs == 0) return PA_OK;
+  if (num_seqs > 65535) return set_error(PA_ERR_INVALID_ARGUMENT, "too many sequences: %d (max 65535)", num_seqs);
+  if (!out || !query || !key_cache || !value_cache || !block_tables || !context_lens)
+    return set_error(PA_ERR_INVALID_ARGUMENT, "null pointer");
+  if ((reinterpret_cast<uintptr_t>(key_cache) | reinterpret_cast<uintptr_t>(value_cache)) & 15u)
+    return set_error(PA_ERR_INVALID_ARGUMENT, "key/value cache must be 16-byte aligned");
+  const int es = dtype_size(dtype);
+  if (reinterpret_cast<uintptr_t>(query) % es || reinterpret_cast<uintptr_t>(out) % es)
+    return set_error(PA_ERR_INVALID_ARGUMENT, "query/out are not element-aligned");
+
+  pa_decode_tuning t = {0, 0, 0, 0};
+  if (tuning) t = *tuning;
+  if (t.variant < 0 || t.variant > 2) return set_error(PA_ERR_INVALID_ARGUMENT, "invalid variant %d", t.variant);
+  int pps = 0;
+  rc = make_plan(num_seqs, num_heads, head_size, block_size, max_context_len, dtype, &t, &pps);
+  if (rc != PA_OK) return rc;
+
+  DecodeLaunch l;
+  std::memset(&l, 0, sizeof(l));
+  DecodeParams& p = l.params;
+  p.out = out; p.q = query; p.k_cache = key_cache; p.v_cache = value_cache;
+  p.block_tables = block_tables; p.context_lens = context_lens;
+  p.q_stride = q_stride;
+  p.scale_log2 = scale * 1.4426950408889634f;
+  p.num_heads = num_heads;
+  p.max_blocks_per_seq = max_num_blocks_per_seq;
+  p.pages_per_split = pps;
+  p.num_splits = t.num_splits;
+  p.num_stages = t.num_stages;
+  p.q_vec_ok = (reinterpret_cast<uintptr_t>(query) % 16 == 0) && ((q_stride * es) % 16 == 0);
+  if (t.num_splits > 1) {
+    const size_t items = static_cast<size_t>(num_seqs) * num_heads;
+    rc = get_workspace(stream, items * sizeof(uint32_t), items * t.num_splits * (head_size + 2) * sizeof(float),
+                       &p.ws_ticket, &p.ws_part);
+    if (rc != PA_OK) return rc;
+  }
+  l.num_seqs = num_seqs; l.head_size = head_size; l.block_size = block_size;
+  l.num_warps = t.num_warps; l.staged = (t.variant == 2); l.stream = stream;
+  switch (dtype) {
+    case PA_F16:  return launch_decode_f16(l);
+    case PA_BF16: return launch_decode_bf16(l);
+    default:      return launch_decode_f32(l);
+  }
+}
+
+}  // namespace pa
+
+extern "C" {
+
+int pa_abi_version(void) { return PA_ABI_VERSION; }
+const char* pa_last_error(void) { return pa::g_err; }
+int pa_compiled_sm(void) { return 100; }
+uint64_t pa_launch_count(void) { return pa::g_launches.load(std::memory_order_relaxed); }
+
+int pa_release_workspaces(void) {
+  int dev = 0;
+  PA_CUDA_TRY(cudaGetDevice(&dev));
+  PA_CUDA_TRY(cudaDeviceSynchronize());
+  std::lock_guard<std::mutex> lock(pa::g_ws_mu);
+  for (auto it = pa::g_ws.begin(); it != pa::g_ws.end();) {
+    if (it->first.first == dev) {
+      if (it->second.ptr) cudaFree(it->second.ptr);
+      it = pa::g_ws.erase(it);
+    } else {
+      ++it;
+    }
+  }
+  return PA_OK;
+}
+
+int pa_decode_attention(void* out, const void* query, const void* key_cache, const void* value_cache,
+                        float scale, const int32_t* block_tables, const int32_t* context_lens,
+                        int32_t num_seqs, int32_t num_heads, int32_t head_size, int32_t block_size,
+                        int32_t max_num_blocks_per_seq, int32_t max_context_len, int64_t q_stride,
+                        int32_t dtype, void* stream) {
+  return pa::decode(out, query, key_cache, value_cache, scale, block_tables, context_lens, num_seqs, num_heads,
+                    head_size, block_size, max_num_blocks_per_seq, max_context_len, q_stride, dtype, nullptr,
+                    static_cast<cudaStream_t>(stream));
+}
+
+int pa_decode_attention_ex(void* out, const void* query, const void* key_cache, const void* value_cache,
+                           float scale, const int32_t* block_tables, const int32_t* context_lens,
+                           int32_t num_seqs, int32_t num_heads, int32_t head_size, int32_t block_size,
+                           int32_t max_num_blocks_per_seq, int32_t max_context_len, int64_t q_stride,
+                           int32_t dtype, const pa_decode_tuning* tuning, void* stream) {
+  return pa::decode(out, query, key_cache, value_cache, scale, block_tables, context_lens, num_seqs, num_heads,
+                    head_size, block_size, max_num_blocks_per_seq, max_context_len, q_stride, dtype, tuning,
+                    static_cast<cudaStream_t>(stream));
+}
+
+int pa_decode_attention_plan(int32_t num_seqs, int32_t num_heads, int32_t head_size, int32_t block_size,
+                             int32_t max_context_len, int32_t dtype, pa_decode_tuning* plan_out) {
+  if (!plan_out) return pa::set_error(PA_ERR_INVALID_ARGUMENT, "plan_out is null");
+  int rc = pa::check_shape(head_size, block_size, dtype);
+  if (rc != PA_OK) return rc;
+  int pps = 0;
+  return pa::make_plan(num_seqs, num_heads, head_size, block_size, max_context_len, dtype, plan_out, &pps);
+}
+
+}  // extern "C"

@@ -1,0 +1,204 @@
+// Shared device helpers for libpaged_b200 (sm_100a only).
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "paged_attention_b200.h"
+
+#if defined(__CUDA_ARCH__) && (__CUDA_ARCH__ < 1000)
+#error "libpaged_b200 is written for sm_100a (B200) only"
+#endif
+
+namespace pa {
+
+// ---------------------------------------------------------------------------
+// host side: error state + launch accounting (defined in pa_api.cu)
+// ---------------------------------------------------------------------------
+int set_error(int code, const char* fmt, ...);
+int check_cuda(cudaError_t e, const char* what);
+void count_launch(uint64_t n = 1);
+
+#define PA_CUDA_TRY(expr)                                      \
+  do {                                                         \
+    int _rc = ::pa::check_cuda((expr), #expr);                 \
+    if (_rc != PA_OK) return _rc;                              \
+  } while (0)
+
+constexpr int kWarp = 32;
+
+inline int dtype_size(int dtype) { return dtype == PA_F32 ? 4 : 2; }
+
+// ---------------------------------------------------------------------------
+// element-type tags.  16-bit types are carried as raw bit patterns; all
+// arithmetic on them goes through the sm_100a mixed-precision FMA below.
+// ---------------------------------------------------------------------------
+struct F16 {
+  static constexpr int kSize = 2;
+  static constexpr int kId = PA_F16;
+};
+struct BF16 {
+  static constexpr int kSize = 2;
+  static constexpr int kId = PA_BF16;
+};
+struct F32 {
+  static constexpr int kSize = 4;
+  static constexpr int kId = PA_F32;
+};
+
+#ifdef __CUDACC__
+
+// d = a.lo * b.lo + c with a, b the low halves of packed 16-bit pairs.
+// sm_100a FHFMA: binary16/bfloat16 operands, fp32 accumulate, exact product,
+// one rounding -- no separate conversion instruction.
+template <typename T>
+__device__ __forceinline__ float mixfma_lo(uint32_t a, uint32_t b, float c);
+template <typename T>
+__device__ __forceinline__ float mixfma_hi(uint32_t a, uint32_t b, float c);
+
+template <>
+__device__ __forceinline__ float mixfma_lo<F16>(uint32_t a, uint32_t b, float c) {
+  float d;
+  asm("{.reg .b16 al, ah, bl, bh;\n\t"
+      "mov.b32 {al, ah}, %1; mov.b32 {bl, bh}, %2;\n\t"
+      "fma.rn.f32.f16 %0, al, bl, %3;}"
+      : "=f"(d) : "r"(a), "r"(b), "f"(c));
+  return d;
+}
+template <>
+__device__ __forceinline__ float mixfma_hi<F16>(uint32_t a, uint32_t b, float c) {
+  float d;
+  asm("{.reg .b16 al, ah, bl, bh;\n\t"
+      "mov.b32 {al, ah}, %1; mov.b32 {bl, bh}, %2;\n\t"
+      "fma.rn.f32.f16 %0, ah, bh, %3;}"
+      : "=f"(d) : "r"(a), "r"(b), "f"(c));
+  return d;
+}
+template <>
+__device__ __forceinline__ float mixfma_lo<BF16>(uint32_t a, uint32_t b, float c) {
+  float d;
+  asm("{.reg .b16 al, ah, bl, bh;\n\t"
+      "mov.b32 {al, ah}, %1; mov.b32 {bl, bh}, %2;\n\t"
+      "fma.rn.f32.bf16 %0, al, bl, %3;}"
+      : "=f"(d) : "r"(a), "r"(b), "f"(c));
+  return d;
+}
+template <>
+__device__ __forceinline__ float mixfma_hi<BF16>(uint32_t a, uint32_t b, float c) {
+  float d;
+  asm("{.reg .b16 al, ah, bl, bh;\n\t"
+      "mov.b32 {al, ah}, %1; mov.b32 {bl, bh}, %2;\n\t"
+      "fma.rn.f32.bf16 %0, ah, bh, %3;}"
+      : "=f"(d) : "r"(a), "r"(b), "f"(c));
+  return d;
+}
+
+// fp32 pair -> packed 16-bit pair, round to nearest even (lo in bits 0-15).
+template <typename T>
+__device__ __forceinline__ uint32_t pack2(float lo, float hi);
+template <>
+__device__ __forceinline__ uint32_t pack2<F16>(float lo, float hi) {
+  uint32_t r;
+  asm("cvt.rn.f16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+  return r;
+}
+template <>
+__device__ __forceinline__ uint32_t pack2<BF16>(float lo, float hi) {
+  uint32_t r;
+  asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+  return r;
+}
+
+// low / high 16-bit element of a packed pair -> fp32 (exact).
+template <typename T>
+__device__ __forceinline__ float unpack_lo(uint32_t v);
+template <typename T>
+__device__ __forceinline__ float unpack_hi(uint32_t v);
+template <>
+__device__ __forceinline__ float unpack_lo<F16>(uint32_t v) {
+  float f;
+  asm("{.reg .b16 l, h; mov.b32 {l, h}, %1; cvt.f32.f16 %0, l;}" : "=f"(f) : "r"(v));
+  return f;
+}
+template <>
+__device__ __forceinline__ float unpack_hi<F16>(uint32_t v) {
+  float f;
+  asm("{.reg .b16 l, h; mov.b32 {l, h}, %1; cvt.f32.f16 %0, h;}" : "=f"(f) : "r"(v));
+  return f;
+}
+template <>
+__device__ __forceinline__ float unpack_lo<BF16>(uint32_t v) {
+  return __uint_as_float(v << 16);
+}
+template <>
+__device__ __forceinline__ float unpack_hi<BF16>(uint32_t v) {
+  return __uint_as_float(v & 0xffff0000u);
+}
+
+// ---------------------------------------------------------------------------
+// warp collectives
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ float warp_max(float v) {
+  float m;  // sm_100a: single-instruction fp32 warp max (CREDUX.MAX.F32)
+  asm volatile("redux.sync.max.f32 %0, %1, 0xffffffff;" : "=f"(m) : "f"(v));
+  return m;
+}
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o >= 1; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+// ---------------------------------------------------------------------------
+// streaming global access: 16-byte, no L1 allocation (every KV byte is read
+// exactly once per call)
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ uint4 ldg_stream(const void* p) {
+  uint4 r;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0, %1, %2, %3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+  return r;
+}
+__device__ __forceinline__ void stg_stream(void* p, const uint4& v) {
+  asm volatile("st.global.L1::no_allocate.v4.u32 [%0], {%1, %2, %3, %4};"
+               :: "l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+
+// ---------------------------------------------------------------------------
+// mbarrier + bulk async copy (TMA engine, no tensor map: pages are contiguous)
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_addr(const void* p) {
+  return static_cast<uint32_t>(__cvta_generic_to_shared(p));
+}
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" :: "r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_init_fence() {
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;"
+               :: "r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "WAIT_%=:\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+      "@p bra DONE_%=;\n\t"
+      "bra WAIT_%=;\n\t"
+      "DONE_%=:\n\t}"
+      :: "r"(bar), "r"(parity) : "memory");
+}
+// global -> this CTA's shared memory, completion counted on `bar`.
+__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t bytes,
+                                         uint32_t bar) {
+  asm volatile(
+      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+      :: "r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
+}
+
+#endif  // __CUDACC__
+
+}  // namespace pa
