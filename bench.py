@@ -1,0 +1,438 @@
+#!/usr/bin/env python
+"""Benchmark of the PagedAttention decode path (BASELINE.json metric).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload NAME] [--impl ours|reference]
+
+A "step" is one decode-attention pass over one batch of synthetic paged KV (random K/V pages,
+every page scattered through a random block table).  The default workload for every N is
+BASELINE.json configs[2], the one the metric's "1/2/4/8 B200" refers to: LLaMA-13B decode,
+40 heads x 128, 256 sequences x 2048-token context, bf16, heads sharded over the N GPUs
+(40/N per GPU, replicated block tables, no collective on the path) -> "scaling": "strong".
+At N=1 the line also carries configs[1] (LLaMA-7B, fp16) under "also".
+
+Prints ONE JSON line (rank 0).  See DESIGN.md "Measurement" for how each field is obtained.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "PagedAttention decode HBM GB/s (% of ~8 TB/s) and seqs/s at 1/2/4/8 B200"
+NOMINAL_HBM_GBS = 8000.0
+FALLBACK_HBM_GBS = 6650.0      # /opt/skills/guides/B200_PROFILING.md, used only without MEASURED_PEAKS.json
+
+# name -> total heads, head size, block size, sequences, context, dtype, sharded over GPUs?
+WORKLOADS = {
+    "llama13b_tp": dict(heads=40, head_size=128, block_size=16, seqs=256, ctx=2048, dtype="bf16", shard=True,
+                        note="BASELINE.json configs[2]: LLaMA-13B paged decode head-sharded at 1/2/4/8 B200"),
+    "llama7b": dict(heads=32, head_size=128, block_size=16, seqs=256, ctx=1024, dtype="fp16", shard=True,
+                    note="BASELINE.json configs[1]: LLaMA-7B decode attention on 1 B200"),
+    "neox20b_tp8": dict(heads=8, head_size=96, block_size=16, seqs=64, ctx=8192, dtype="fp16", shard=False,
+                        note="BASELINE.json configs[4]: GPT-NeoX-20B per-GPU shape at TP=8 (8 heads x 96)"),
+    "opt66b_tp8": dict(heads=9, head_size=128, block_size=16, seqs=64, ctx=8192, dtype="fp16", shard=False,
+                       note="BASELINE.json configs[4]: OPT-66B per-GPU shape at TP=8 (9 heads x 128)"),
+}
+
+
+def _torch_dtype(name):
+    import torch
+    return {"fp16": torch.float16, "bf16": torch.bfloat16, "fp32": torch.float32}[name]
+
+
+def algorithmic_bytes(seqs, heads, head_size, block_size, ctx, esize):
+    """K and V of exactly ctx tokens per head, q read + out write per head,
+    the used block-table entries and the context length once per sequence."""
+    per_seq = heads * (2 * ctx * head_size * esize + 2 * head_size * esize) + ((ctx + block_size - 1) // block_size) * 4 + 4
+    return seqs * per_seq
+
+
+def measured_peak():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    try:
+        with open(path) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs, copy read+write)"
+    except Exception:
+        return FALLBACK_HBM_GBS, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+# ---------------------------------------------------------------------------
+# clocks and throttle reasons during the timed region (NVML, the source nvidia-smi reads)
+# ---------------------------------------------------------------------------
+class ClockSampler(threading.Thread):
+    REASONS = {0x4: "sw_power_cap", 0x8: "hw_slowdown", 0x20: "sw_thermal_slowdown", 0x40: "hw_thermal_slowdown",
+               0x80: "hw_power_brake_slowdown", 0x2: "applications_clocks_setting", 0x10: "sync_boost"}
+
+    def __init__(self, device_index: int, period_s: float = 0.01):
+        super().__init__(daemon=True)
+        self.period = period_s
+        self.samples = []          # (wall time, sm MHz, reasons bitmask, power W)
+        self.stop_flag = threading.Event()
+        self.handle = None
+        self.max_mhz = None
+        try:
+            import pynvml
+            import torch
+            self.nv = pynvml
+            pynvml.nvmlInit()
+            try:
+                uuid = "GPU-" + str(torch.cuda.get_device_properties(device_index).uuid)
+                self.handle = pynvml.nvmlDeviceGetHandleByUUID(uuid)
+            except Exception:
+                vis = os.environ.get("CUDA_VISIBLE_DEVICES", "")
+                idx = int(vis.split(",")[device_index]) if vis and vis.split(",")[device_index].isdigit() else device_index
+                self.handle = pynvml.nvmlDeviceGetHandleByIndex(idx)
+            self.max_mhz = int(pynvml.nvmlDeviceGetMaxClockInfo(self.handle, pynvml.NVML_CLOCK_SM))
+        except Exception as e:     # no NVML: the clocks object says so
+            self.error = repr(e)
+            self.handle = None
+
+    def run(self):
+        if self.handle is None:
+            return
+        nv = self.nv
+        while not self.stop_flag.is_set():
+            try:
+                mhz = int(nv.nvmlDeviceGetClockInfo(self.handle, nv.NVML_CLOCK_SM))
+                try:
+                    rs = int(nv.nvmlDeviceGetCurrentClocksEventReasons(self.handle))
+                except Exception:
+                    rs = int(nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.handle))
+                try:
+                    pw = nv.nvmlDeviceGetPowerUsage(self.handle) / 1000.0
+                except Exception:
+                    pw = None
+                self.samples.append((time.perf_counter(), mhz, rs, pw))
+            except Exception:
+                pass
+            time.sleep(self.period)
+
+    def summary(self, windows):
+        """Median SM clock and the union of throttle reasons over samples inside the timed windows."""
+        if self.handle is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "error": getattr(self, "error", "no NVML")}
+        inside = [s for s in self.samples if any(a <= s[0] <= b for a, b in windows)]
+        use = inside if inside else self.samples
+        clocks = sorted(s[1] for s in use)
+        bits = 0
+        for s in use:
+            bits |= s[2]
+        reasons = [name for bit, name in self.REASONS.items() if bits & bit]
+        powers = [s[3] for s in use if s[3] is not None]
+        return {"sm_mhz": clocks[len(clocks) // 2] if clocks else None, "sm_max_mhz": self.max_mhz,
+                "reasons": reasons, "samples": len(inside), "power_w_max": max(powers) if powers else None}
+
+
+# ---------------------------------------------------------------------------
+# synthetic problem on the device
+# ---------------------------------------------------------------------------
+def make_problem(wl, heads_local, device, seed=0):
+    """Random KV pages for `heads_local` heads; block tables are a random permutation of all
+    blocks (identical on every rank: same seed), so every page is a scattered chunk."""
+    import torch
+    dtype = _torch_dtype(wl["dtype"])
+    S, D, B, L = wl["seqs"], wl["head_size"], wl["block_size"], wl["ctx"]
+    x = 16 // torch.empty((), dtype=dtype).element_size()
+    nblk = (L + B - 1) // B
+    NB = S * nblk
+    g = torch.Generator(device=device).manual_seed(seed)
+    kc = torch.empty((NB, heads_local, D // x, B, x), dtype=dtype, device=device).normal_(generator=g)
+    vc = torch.empty((NB, heads_local, D, B), dtype=dtype, device=device).normal_(generator=g)
+    qkv = torch.empty((S, 3, heads_local, D), dtype=dtype, device=device).normal_(generator=g)
+    gt = torch.Generator().manual_seed(seed)            # host generator: same tables on every rank
+    tables = torch.randperm(NB, generator=gt).to(torch.int32).view(S, nblk).contiguous()
+    lens = torch.full((S,), L, dtype=torch.int32)
+    return dict(q=qkv[:, 0], kc=kc, vc=vc, tables=tables.to(device), lens=lens.to(device), tables_host=tables,
+                lens_host=lens, scale=float(D) ** -0.5, B=B, L=L, dtype=dtype)
+
+
+def run_kernel_steps(p, steps, warmup, barrier):
+    """W untimed + K timed calls of the operator on device-resident inputs; returns (ms total, wall window, launches)."""
+    import torch
+    from vllm_b200 import _cabi, attention_ops
+    out = torch.empty(p["q"].shape, dtype=p["dtype"], device=p["q"].device)
+
+    def step():
+        attention_ops.single_query_cached_kv_attention(out, p["q"], p["kc"], p["vc"], p["scale"], p["tables"],
+                                                       p["lens"], p["B"], p["L"])
+    for _ in range(warmup):
+        step()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    torch.cuda.synchronize()
+    n0 = _cabi.launch_count()
+    t0 = time.perf_counter()
+    e0.record()
+    for _ in range(steps):
+        step()
+    e1.record()
+    torch.cuda.synchronize()
+    t1 = time.perf_counter()
+    barrier()
+    return e0.elapsed_time(e1), (t0, t1), _cabi.launch_count() - n0, out
+
+
+def run_e2e_steps(p, steps, warmup, barrier):
+    """The same operator called the way a worker calls it each decode step, from HOST buffers:
+    every step copies that step's inputs (query, block tables, context lengths) from pinned host
+    memory to the device, runs the operator and reads the result back to pinned host memory.
+    The KV cache is the worker's resident state (vllm/worker/cache_engine.py allocates it on the
+    GPU once); it is not a per-step input."""
+    import torch
+    from vllm_b200 import attention_ops
+    dev = p["q"].device
+    q_host = p["q"].contiguous().cpu().pin_memory()
+    t_host = p["tables_host"].pin_memory()
+    l_host = p["lens_host"].pin_memory()
+    out_host = torch.empty(q_host.shape, dtype=p["dtype"]).pin_memory()
+    q_dev, t_dev, l_dev = torch.empty_like(q_host, device=dev), torch.empty_like(t_host, device=dev), \
+        torch.empty_like(l_host, device=dev)
+    out_dev = torch.empty_like(q_dev)
+    h2d = q_host.numel() * q_host.element_size() + t_host.numel() * 4 + l_host.numel() * 4
+    d2h = out_host.numel() * out_host.element_size()
+
+    def step():
+        q_dev.copy_(q_host, non_blocking=True)
+        t_dev.copy_(t_host, non_blocking=True)
+        l_dev.copy_(l_host, non_blocking=True)
+        attention_ops.single_query_cached_kv_attention(out_dev, q_dev, p["kc"], p["vc"], p["scale"], t_dev, l_dev,
+                                                       p["B"], p["L"])
+        out_host.copy_(out_dev, non_blocking=True)
+        torch.cuda.current_stream().synchronize()          # the host has this step's result
+
+    for _ in range(warmup):
+        step()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    e0.record()
+    for _ in range(steps):
+        step()
+    e1.record()
+    torch.cuda.synchronize()
+    t1 = time.perf_counter()
+    barrier()
+    return e0.elapsed_time(e1), (t0, t1), h2d, d2h
+
+
+# ---------------------------------------------------------------------------
+# CPU side: the reference's PyTorch path (restated in oracle/paged_oracle.py) on host cores
+# ---------------------------------------------------------------------------
+def make_host_sample(wl, nseq, seed=0):
+    """`nseq` sequences of the workload with ALL heads, on the host, compact cache (only their pages)."""
+    import torch
+    dtype = _torch_dtype(wl["dtype"])
+    H, D, B, L = wl["heads"], wl["head_size"], wl["block_size"], wl["ctx"]
+    x = 16 // torch.empty((), dtype=dtype).element_size()
+    nblk = (L + B - 1) // B
+    NB = nseq * nblk
+    g = torch.Generator().manual_seed(seed)
+    # uniform values are as good as normal ones for timing and much cheaper to draw
+    kc = (torch.rand((NB, H, D // x, B, x), generator=g) - 0.5).to(dtype)
+    vc = (torch.rand((NB, H, D, B), generator=g) - 0.5).to(dtype)
+    q = (torch.rand((nseq, H, D), generator=g) - 0.5).to(dtype)
+    tables = torch.randperm(NB, generator=g).to(torch.int32).view(nseq, nblk).contiguous()
+    lens = torch.full((nseq,), L, dtype=torch.int32)
+    return q, kc, vc, tables, lens
+
+
+def time_cpu_reference(wl, nseq, steps=1, warmup=0):
+    """seconds per pass of the PyTorch loop oracle over `nseq` sequences (all heads, full context)."""
+    import torch
+    from oracle import paged_oracle
+    q, kc, vc, tables, lens = make_host_sample(wl, nseq)
+    out = torch.empty_like(q)
+    for _ in range(warmup):
+        paged_oracle.decode_attention_loop(out, q, kc, vc, tables, lens)
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        paged_oracle.decode_attention_loop(out, q, kc, vc, tables, lens)
+    return (time.perf_counter() - t0) / steps
+
+
+def cpu_sample_size(wl, budget_s, cap):
+    """Sequences per CPU pass so that one pass takes about `budget_s` (calibrated on one sequence)."""
+    one = time_cpu_reference(wl, 1)
+    return max(1, min(cap, int(budget_s / max(one, 1e-3)))), one
+
+
+def workload_config(name, wl, n_gpus, heads_local):
+    return {"workload": name, "note": wl["note"], "num_seqs": wl["seqs"], "total_heads": wl["heads"],
+            "heads_per_gpu": heads_local, "head_size": wl["head_size"], "block_size": wl["block_size"],
+            "context_len": wl["ctx"], "kv_dtype": wl["dtype"],
+            "parallelism": f"heads sharded over {n_gpus} GPU(s), no collective" if wl["shard"] else f"{n_gpus} replica(s)"}
+
+
+def run_reference(args, wl):
+    """--impl reference: the reference's own CPU implementation of the path (its PyTorch test
+    reference, restated in oracle/paged_oracle.py because /root/reference is absent on the GPU box),
+    all host threads, each step a bounded sample of the workload."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    import torch
+    nseq, one = cpu_sample_size(wl, budget_s=120.0 / max(1, args.steps + args.warmup), cap=16)
+    sec = time_cpu_reference(wl, nseq, steps=args.steps, warmup=args.warmup)
+    value = nseq / sec
+    esize = 2 if wl["dtype"] != "fp32" else 4
+    gbs = algorithmic_bytes(nseq, wl["heads"], wl["head_size"], wl["block_size"], wl["ctx"], esize) / sec / 1e9
+    sample = f"{nseq} of {wl['seqs']} sequences per step (all {wl['heads']} heads, {wl['ctx']}-token contexts)"
+    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": "seqs/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": sec * 1e3, "higher_is_better": True,
+            "scaling": "strong" if wl["shard"] else "weak", "vs_baseline": None, "dtype": wl["dtype"],
+            "data": "synthetic", "hbm_gbs": gbs,
+            "config": workload_config(args.workload, wl, args.gpus, wl["heads"]),
+            "cpu_baseline": {"value": value, "unit": "seqs/s", "cores": torch.get_num_threads(), "kind": "port",
+                             "sample": sample, "host_cpus": os.cpu_count()},
+            "e2e": {"value": value, "unit": "seqs/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+def traffic_from_profiles(workload):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed ncu --set full
+    capture of this workload's kernel (profiles/roofline_traffic.json), or None."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "roofline_traffic.json")) as f:
+            return json.load(f).get(workload, {}).get("dram_bytes_per_launch")
+    except Exception:
+        return None
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=20)
+    ap.add_argument("--workload", default="llama13b_tp", choices=sorted(WORKLOADS))
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--no-cpu-baseline", action="store_true", help="skip the CPU leg (tuning runs)")
+    ap.add_argument("--no-also", action="store_true", help="skip the extra configs[1] measurement at N=1")
+    args = ap.parse_args()
+    if args.warmup < 3:
+        args.warmup = 3
+    wl = WORKLOADS[args.workload]
+
+    if args.impl == "reference":
+        run_reference(args, wl)
+        return
+
+    import torch
+    import torch.distributed as dist
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a GPU: the product path has no CPU fallback (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+    n_gpus = world
+    if args.gpus != world and rank == 0:
+        print(f"[bench] --gpus {args.gpus} but WORLD_SIZE={world}; using {world}", file=sys.stderr)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+
+    def max_over_ranks(ms):
+        if world == 1:
+            return ms
+        t = torch.tensor([ms], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    if wl["shard"]:
+        assert wl["heads"] % n_gpus == 0, "total heads must divide by the GPU count (vllm/config.py:54-60)"
+        heads_local = wl["heads"] // n_gpus
+    else:
+        heads_local = wl["heads"]
+
+    from vllm_b200 import _cabi
+    _cabi.lib()                                       # fails loudly if libpaged_b200.so is missing
+    sampler = ClockSampler(local)
+    sampler.start()
+
+    p = make_problem(wl, heads_local, dev)
+    esize = p["kc"].element_size()
+    ms_k, win_k, launches, _ = run_kernel_steps(p, args.steps, args.warmup, barrier)
+    ms_k = max_over_ranks(ms_k)
+    ms_e, win_e, h2d, d2h = run_e2e_steps(p, args.steps, args.warmup, barrier)
+    ms_e = max_over_ranks(ms_e)
+
+    total_heads = wl["heads"] if wl["shard"] else wl["heads"] * n_gpus
+    seqs_job = wl["seqs"] if wl["shard"] else wl["seqs"] * n_gpus      # sequences the whole job finishes per step
+    t_step = ms_k / args.steps / 1e3
+    t_e2e = ms_e / args.steps / 1e3
+    bytes_gpu = algorithmic_bytes(wl["seqs"], heads_local, wl["head_size"], wl["block_size"], wl["ctx"], esize)
+    bytes_job = bytes_gpu * n_gpus
+    peak, peak_src = measured_peak()
+    achieved = bytes_gpu / t_step / 1e9
+    kv_gb = 2 * p["kc"].numel() * esize / 1e9
+
+    also = None
+    if n_gpus == 1 and args.workload == "llama13b_tp" and not args.no_also:
+        del p
+        torch.cuda.empty_cache()
+        wl2 = WORKLOADS["llama7b"]
+        p2 = make_problem(wl2, wl2["heads"], dev)
+        ms2, win2, _, _ = run_kernel_steps(p2, args.steps, args.warmup, barrier)
+        ms2e, win2e, _, _ = run_e2e_steps(p2, args.steps, args.warmup, barrier)
+        b2 = algorithmic_bytes(wl2["seqs"], wl2["heads"], wl2["head_size"], wl2["block_size"], wl2["ctx"], 2)
+        t2 = ms2 / args.steps / 1e3
+        also = {"config": workload_config("llama7b", wl2, 1, wl2["heads"]), "dtype": "fp16",
+                "value": wl2["seqs"] / t2, "unit": "seqs/s", "ms_per_step": t2 * 1e3, "hbm_gbs": b2 / t2 / 1e9,
+                "roofline_frac_of_measured": b2 / t2 / 1e9 / peak, "frac_of_8tbs": b2 / t2 / 1e9 / NOMINAL_HBM_GBS,
+                "e2e_value": wl2["seqs"] / (ms2e / args.steps / 1e3)}
+        del p2
+        torch.cuda.empty_cache()
+
+    sampler.stop_flag.set()
+    sampler.join(timeout=2)
+    clocks = sampler.summary([win_k, win_e])
+
+    cpu_baseline = None
+    if rank == 0 and n_gpus == 1 and not args.no_cpu_baseline:
+        nseq, one = cpu_sample_size(wl, budget_s=15.0, cap=64)
+        sec = time_cpu_reference(wl, nseq)
+        cpu_baseline = {"value": nseq / sec, "unit": "seqs/s", "cores": torch.get_num_threads(), "kind": "port",
+                        "sample": f"one pass over {nseq} of {wl['seqs']} sequences (all {wl['heads']} heads, "
+                                  f"{wl['ctx']}-token contexts), PyTorch loop reference restated in oracle/paged_oracle.py",
+                        "seconds": sec, "host_cpus": os.cpu_count()}
+
+    if rank == 0:
+        line = {
+            "metric": METRIC, "value": seqs_job / t_step, "unit": "seqs/s", "n_gpus": n_gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": t_step * 1e3, "higher_is_better": True,
+            "scaling": "strong" if wl["shard"] else "weak", "vs_baseline": None, "dtype": wl["dtype"],
+            "data": "synthetic",
+            "config": dict(workload_config(args.workload, wl, n_gpus, heads_local),
+                           l2=f"inputs larger than L2: {kv_gb:.2f} GB of KV pages per GPU re-read every step vs 126 MB L2"),
+            "hbm_gbs": bytes_job / t_step / 1e9, "hbm_frac_of_8tbs": achieved / NOMINAL_HBM_GBS,
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                         "traffic": traffic_from_profiles(args.workload), "peak_source": peak_src,
+                         "algorithmic_bytes_per_launch": bytes_gpu, "kernel": "pa::paged_decode_kernel"},
+            "e2e": {"value": seqs_job / t_e2e, "unit": "seqs/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                    "ms_per_step": t_e2e * 1e3,
+                    "note": "per step: pinned host query + block tables + context lens -> device, operator, output -> "
+                            "pinned host, stream sync; the KV cache is resident worker state"},
+            "gpu_launches": launches, "clocks": clocks, "cpu_baseline": cpu_baseline,
+        }
+        if also is not None:
+            line["also"] = also
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
