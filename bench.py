@@ -352,8 +352,8 @@ def main():
         return float(t.item())
 
     if wl["shard"]:
-        assert wl["heads"] % n_gpus == 0, "total heads must divide by the GPU count (vllm/config.py:54-60)"
-        heads_local = wl["heads"] // n_gpus
+        from vllm_b200 import sharding
+        heads_local = sharding.heads_per_gpu(wl["heads"], n_gpus)      # raises unless it divides (vllm/config.py:54-60)
     else:
         heads_local = wl["heads"]
 

@@ -7,5 +7,6 @@ not a valid Python identifier).
 """
 from . import _cabi, attention_ops, cache_ops  # noqa: F401
 from .cache_engine import CacheEngine, kv_cache_shapes  # noqa: F401
+from . import sharding  # noqa: F401
 
 __all__ = ["attention_ops", "cache_ops", "CacheEngine", "kv_cache_shapes"]
