@@ -217,12 +217,22 @@ PA_API int pa_copy_blocks(void* const* key_cache_ptrs, void* const* value_cache_
  * dst[dst_blocks[i]] = src[src_blocks[i]] for i < num_blocks, whole blocks of
  * block_bytes.  kind selects device/host sides; host memory may be pageable
  * or pinned (pinned is what vllm/worker/cache_engine.py:88-97 allocates).
- * Runs of consecutive (src, dst) block numbers are merged into one DMA.
  * src_blocks / dst_blocks are HOST arrays.
+ * Few contiguous runs of (src, dst) blocks go through the copy engines, one DMA
+ * per run; many scattered blocks with pinned host memory (or GPU->GPU) go
+ * through one gather/scatter kernel per 240 blocks that accesses the host
+ * buffer directly over PCIe.  Both are stream-ordered and asynchronous.
  */
 PA_API int pa_swap_blocks(const void* src, void* dst, int64_t block_bytes,
                    const int64_t* src_blocks, const int64_t* dst_blocks,
                    int64_t num_blocks, int32_t kind, void* stream);
+
+/* Same with the engine forced: 0 automatic, 1 copy engines, 2 kernel (falls
+ * back to the copy engines when the host side is pageable).  Tests and tuning. */
+PA_API int pa_swap_blocks_ex(const void* src, void* dst, int64_t block_bytes,
+                      const int64_t* src_blocks, const int64_t* dst_blocks,
+                      int64_t num_blocks, int32_t kind, int32_t engine,
+                      void* stream);
 
 #ifdef __cplusplus
 } /* extern "C" */

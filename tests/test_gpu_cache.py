@@ -127,15 +127,19 @@ def test_copy_blocks(dtype, layers, pairs, heads, head_size, block_size, nb):
         assert _same_bits(dk[l], kcs[l]) and _same_bits(dv[l], vcs[l]), f"layer {l}"
 
 
-def test_swap_blocks_round_trip_and_directions():
-    """swap_blocks is unpinned by the reference (no test there): pinned here on block assignment."""
-    from vllm_b200 import cache_ops
+@pytest.mark.parametrize("engine", [0, 1, 2])
+def test_swap_blocks_round_trip_and_directions(engine):
+    """swap_blocks is unpinned by the reference (no test there): pinned here on block assignment
+    (and on the reference's implementation in test_gpu_vs_reference_kernels.py), for both engines."""
+    from vllm_b200 import cache_ops as _ops
+    import types
+    cache_ops = types.SimpleNamespace(swap_blocks=lambda s, d, m: _ops.swap_blocks(s, d, m, engine=engine))
     nb, heads, d, b = 64, 5, 128, 16
     g = torch.Generator().manual_seed(1)
     gpu = torch.randn((nb, heads, d, b), generator=g).to(torch.float16).to(DEV)
     cpu = torch.randn((nb, heads, d, b), generator=g).to(torch.float16).pin_memory()
     gpu0, cpu0 = gpu.clone(), cpu.clone()
-    out_map = {3: 7, 4: 8, 5: 9, 20: 0, 63: 62, 10: 11}          # runs (3,4,5)->(7,8,9) merge into one DMA
+    out_map = {3: 7, 4: 8, 5: 9, 20: 0, 63: 62, 10: 11, 30: 33, 40: 35, 50: 37}   # (3,4,5)->(7,8,9) merges into one DMA
     cache_ops.swap_blocks(gpu, cpu, out_map)                      # GPU -> CPU
     torch.cuda.synchronize()
     want = cpu0.clone()
@@ -155,5 +159,38 @@ def test_swap_blocks_round_trip_and_directions():
     cache_ops.swap_blocks(gpu0, pageable, {9: 1})                 # pageable host memory also works
     torch.cuda.synchronize()
     assert torch.equal(pageable[1], gpu0[9].cpu())
+    many = {i: (i * 7) % nb for i in range(0, nb, 2)}             # > 6 runs: the automatic choice is the kernel
+    pageable.zero_()
+    cache_ops.swap_blocks(gpu0, pageable, many)                   # ... which falls back to DMA for pageable memory
+    torch.cuda.synchronize()
+    for s_blk, d_blk in many.items():
+        assert torch.equal(pageable[d_blk], gpu0[s_blk].cpu())
     with pytest.raises(RuntimeError, match="Invalid device combination"):
-        cache_ops.swap_blocks(pageable, pageable.clone(), {0: 1})
+        _ops.swap_blocks(pageable, pageable.clone(), {0: 1})
+
+
+def test_reshape_and_cache_prefill_runs_and_padding_tokens():
+    """Consecutive slots (a prompt filling its blocks in order), runs crossing block boundaries, a ragged
+    last tile, and negative slots (skipped)."""
+    from vllm_b200 import cache_ops
+    for dtype in (torch.float16, torch.float32):
+        x = pt.pack_factor(dtype)
+        n, h, d, b, nb = 203, 3, 128, 16, 40
+        g = torch.Generator().manual_seed(7)
+        qkv = torch.randn((n, 3, h, d), generator=g).to(dtype)
+        kc = torch.randn((nb, h, d // x, b, x), generator=g).to(dtype)
+        vc = torch.randn((nb, h, d, b), generator=g).to(dtype)
+        # three prompts: 100 tokens from slot 37, 60 from slot 320, 43 scattered; a few padding tokens
+        slots = torch.cat([torch.arange(37, 137), torch.arange(320, 380),
+                           torch.randperm(200, generator=g)[:43] + 400]).to(torch.int32)
+        slots[[5, 101, 202]] = -1
+        wk, wv = kc.clone(), vc.clone()
+        c_oracle.reshape_and_cache(qkv[:, 1], qkv[:, 2], wk, wv, slots)
+        dq, dk, dv = qkv.to(DEV), kc.to(DEV), vc.to(DEV)
+        cache_ops.reshape_and_cache(dq[:, 1], dq[:, 2], dk, dv, slots.to(DEV))
+        assert _same_bits(dk, wk) and _same_bits(dv, wv)
+        back = torch.zeros_like(dq)
+        cache_ops.gather_cached_kv(back[:, 1], back[:, 2], dk, dv, slots.to(DEV))
+        want = torch.zeros_like(qkv)
+        c_oracle.gather_cached_kv(want[:, 1], want[:, 2], wk, wv, slots)
+        assert _same_bits(back, want)

@@ -56,9 +56,15 @@ def test_decode_attention_matches_reference_kernel(ref_attention, dtype, block_s
     ref_attention.single_query_cached_kv_attention(theirs, p.query, p.key_cache, p.value_cache, p.scale,
                                                    p.block_tables, p.context_lens, block_size, p.max_context_len)
     torch.cuda.synchronize()
-    pt.assert_decode_close(ours, theirs, dtype, f"vs reference kernel {dtype} B{block_size} D{head_size} {dist}")
-    if dist == "ref":           # the reference test's own criterion (test_attention.py:224)
+    if dist == "ref":
+        # the reference test's own criterion (test_attention.py:224).  On these U(+-1e-3) inputs the reference
+        # kernel's fp16 P.V products (p*v ~ 1e-7) fall into fp16 subnormals, so it is itself only good to a few
+        # percent of the output scale there; ours is held to 1e-3 of the fp64 oracle in test_gpu_decode.py.
         assert torch.allclose(ours, theirs, atol=1e-3, rtol=1e-5)
+        scale = float(theirs.float().abs().max())
+        assert float((ours.float() - theirs.float()).abs().max()) <= 0.05 * scale
+    else:
+        pt.assert_decode_close(ours, theirs, dtype, f"vs reference kernel {dtype} B{block_size} D{head_size} {dist}")
 
 
 def test_decode_attention_config2_matches_reference_kernel(ref_attention):
@@ -90,6 +96,8 @@ def test_reshape_and_gather_bit_exact_vs_reference_kernel(ref_cache, dtype, toke
     kc = torch.empty((nb, heads, head_size // x, block_size, x), dtype=dtype, device=DEV).normal_(generator=g)
     vc = torch.empty((nb, heads, head_size, block_size), dtype=dtype, device=DEV).normal_(generator=g)
     slots = torch.randperm(nb * block_size, generator=g, device=DEV)[:tokens].to(torch.int32)
+    if tokens % 2 == 0:       # prefill-like: consecutive slots from a random start (runs cross block boundaries)
+        slots = (torch.arange(tokens, device=DEV, dtype=torch.int32) + 5) % (nb * block_size)
     kc_r, vc_r = kc.clone(), vc.clone()
     ref_cache.reshape_and_cache(qkv[:, 1], qkv[:, 2], kc_r, vc_r, slots)
     cache_ops.reshape_and_cache(qkv[:, 1], qkv[:, 2], kc, vc, slots)
@@ -127,18 +135,19 @@ def test_swap_blocks_bit_exact_vs_reference_implementation(ref_cache):
     nb, heads, d, b = 48, 5, 128, 16
     gpu = torch.randn((nb, heads, d, b), device=DEV).half()
     cpu = torch.randn((nb, heads, d, b)).half().pin_memory()
-    out_map = {3: 7, 4: 8, 5: 9, 20: 0, 47: 46, 10: 11, 30: 2}
-    cpu_r, cpu_o = cpu.clone().pin_memory(), cpu.clone().pin_memory()
-    ref_cache.swap_blocks(gpu, cpu_r, out_map)
-    cache_ops.swap_blocks(gpu, cpu_o, out_map)
-    torch.cuda.synchronize()
-    assert torch.equal(pt.bits(cpu_r), pt.bits(cpu_o))
-    gpu_r, gpu_o = gpu.clone(), gpu.clone()
-    in_map = {7: 1, 8: 2, 9: 3, 0: 40, 46: 47}
-    ref_cache.swap_blocks(cpu, gpu_r, in_map)
-    cache_ops.swap_blocks(cpu, gpu_o, in_map)
-    assert torch.equal(pt.bits(gpu_r), pt.bits(gpu_o))
-    d_r, d_o = torch.zeros_like(gpu), torch.zeros_like(gpu)
-    ref_cache.swap_blocks(gpu, d_r, {1: 2, 2: 1, 40: 41})
-    cache_ops.swap_blocks(gpu, d_o, {1: 2, 2: 1, 40: 41})
-    assert torch.equal(pt.bits(d_r), pt.bits(d_o))
+    out_map = {3: 7, 4: 8, 5: 9, 20: 0, 47: 46, 10: 11, 30: 2, 33: 31, 35: 21, 37: 23}
+    for engine in (0, 1, 2):             # automatic, copy engines, zero-copy kernel
+        cpu_r, cpu_o = cpu.clone().pin_memory(), cpu.clone().pin_memory()
+        ref_cache.swap_blocks(gpu, cpu_r, out_map)
+        cache_ops.swap_blocks(gpu, cpu_o, out_map, engine=engine)
+        torch.cuda.synchronize()
+        assert torch.equal(pt.bits(cpu_r), pt.bits(cpu_o)), f"gpu->cpu engine {engine}"
+        gpu_r, gpu_o = gpu.clone(), gpu.clone()
+        in_map = {7: 1, 8: 2, 9: 3, 0: 40, 46: 47, 11: 13, 21: 15, 23: 17}
+        ref_cache.swap_blocks(cpu, gpu_r, in_map)
+        cache_ops.swap_blocks(cpu, gpu_o, in_map, engine=engine)
+        assert torch.equal(pt.bits(gpu_r), pt.bits(gpu_o)), f"cpu->gpu engine {engine}"
+        d_r, d_o = torch.zeros_like(gpu), torch.zeros_like(gpu)
+        ref_cache.swap_blocks(gpu, d_r, {1: 2, 2: 1, 40: 41})
+        cache_ops.swap_blocks(gpu, d_o, {1: 2, 2: 1, 40: 41}, engine=engine)
+        assert torch.equal(pt.bits(d_r), pt.bits(d_o)), f"gpu->gpu engine {engine}"

@@ -79,7 +79,11 @@ def main():
     print(json.dumps(rows[-1]), flush=True)
     for N in (256, 2560):
         qkv = torch.randn((N, 3, H, D), device=DEV).half()
-        slots = torch.randperm(NB * B, device=DEV)[:N].to(torch.int32)
+        if N <= 256:     # decode step: every token is the newest token of its own sequence -> its own block
+            slots = (torch.randperm(NB, device=DEV)[:N] * B + torch.randint(0, B, (N,), device=DEV)).to(torch.int32)
+        else:            # prefill: prompts of 512 tokens fill consecutive slots of scattered block runs
+            starts = torch.randperm(NB // 32, device=DEV)[:N // 512] * 32 * B
+            slots = (starts[:, None] + torch.arange(512, device=DEV)[None, :]).flatten().to(torch.int32)
         a = time_calls(lambda: cache_ops.reshape_and_cache(qkv[:, 1], qkv[:, 2], kcs[0], vcs[0], slots), iters=50)
         b = time_calls(lambda: ref_cache.reshape_and_cache(qkv[:, 1], qkv[:, 2], kcs[0], vcs[0], slots), iters=50)
         rows.append(dict(op="reshape_and_cache", shape=f"{N} tokens x 40 heads x 128", ours_ms=round(a, 4),

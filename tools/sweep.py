@@ -112,7 +112,11 @@ def sweep_movers():
     # reshape_and_cache: decode step (256 tokens) and prefill (2560 tokens)
     for N in (256, 2560):
         qkv = torch.randn((N, 3, H, D), device=DEV).half()
-        slots = torch.randperm(NB * B, device=DEV)[:N].to(torch.int32)
+        if N <= 256:     # decode step: every token is the newest token of its own sequence -> its own block
+            slots = (torch.randperm(NB, device=DEV)[:N] * B + torch.randint(0, B, (N,), device=DEV)).to(torch.int32)
+        else:            # prefill: prompts of 512 tokens fill consecutive slots of scattered block runs
+            starts = torch.randperm(NB // 32, device=DEV)[:N // 512] * 32 * B
+            slots = (starts[:, None] + torch.arange(512, device=DEV)[None, :]).flatten().to(torch.int32)
         ms = time_calls(lambda: cache_ops.reshape_and_cache(qkv[:, 1], qkv[:, 2], kcs[0], vcs[0], slots), iters=50)
         nbytes = N * H * D * 2 * 2 * 2
         row = dict(op="reshape_and_cache", tokens=N, ms=round(ms, 4), gbs=round(nbytes / ms / 1e6, 1))
@@ -128,13 +132,15 @@ def sweep_movers():
     for nblk, contiguous in ((128, True), (128, False), (512, False)):
         ids = list(range(nblk)) if contiguous else torch.randperm(NB)[:nblk].tolist()
         mapping = {int(s): int(d) for s, d in zip(ids, ids if contiguous else torch.randperm(NB)[:nblk].tolist())}
-        for direction, (src, dst) in (("d2h", (vcs[0], cpu)), ("h2d", (cpu, vcs[0]))):
-            ms = time_calls(lambda: cache_ops.swap_blocks(src, dst, mapping), iters=10, warm=2)
-            nbytes = nblk * H * D * B * 2
-            row = dict(op="swap_blocks", dir=direction, blocks=nblk, contiguous=contiguous, ms=round(ms, 4),
-                       gbs=round(nbytes / ms / 1e6, 1))
-            res.append(row)
-            print(json.dumps(row), flush=True)
+        for direction, (src, dst) in (("d2h", (vcs[0], cpu)), ("h2d", (cpu, vcs[0])), ("d2d", (vcs[0], vcs[1]))):
+            for engine in (1, 2):
+                ms = time_calls(lambda: cache_ops.swap_blocks(src, dst, mapping, engine=engine), iters=10, warm=2)
+                nbytes = nblk * H * D * B * 2
+                row = dict(op="swap_blocks", dir=direction, blocks=nblk, contiguous=contiguous,
+                           engine="copy engines" if engine == 1 else "kernel", ms=round(ms, 4),
+                           gbs=round(nbytes / ms / 1e6, 1))
+                res.append(row)
+                print(json.dumps(row), flush=True)
     return res
 
 

@@ -100,8 +100,10 @@ def copy_blocks(key_caches: List[torch.Tensor], value_caches: List[torch.Tensor]
     _cabi.check(rc)
 
 
-def swap_blocks(src: torch.Tensor, dst: torch.Tensor, block_mapping: Dict[int, int]) -> None:
-    """dst[block_mapping[s]] = src[s] for whole cache blocks; GPU<->GPU (same device), GPU->CPU or CPU->GPU."""
+def swap_blocks(src: torch.Tensor, dst: torch.Tensor, block_mapping: Dict[int, int], *, engine: int = 0) -> None:
+    """dst[block_mapping[s]] = src[s] for whole cache blocks; GPU<->GPU (same device), GPU->CPU or CPU->GPU.
+
+    `engine` (keyword-only, not part of the reference signature): 0 automatic, 1 copy engines, 2 kernel."""
     if src.is_cuda and dst.is_cuda:
         if src.device != dst.device:
             raise RuntimeError("src and dst must be on the same GPU")
@@ -124,6 +126,6 @@ def swap_blocks(src: torch.Tensor, dst: torch.Tensor, block_mapping: Dict[int, i
     srcs = (C.c_int64 * n)(*[int(k) for k in keys])
     dsts = (C.c_int64 * n)(*[int(block_mapping[k]) for k in keys])
     with torch.cuda.device(dev):
-        rc = _cabi.lib().pa_swap_blocks(src.data_ptr(), dst.data_ptr(), block_bytes, srcs, dsts, n, kind,
-                                        torch.cuda.current_stream(dev).cuda_stream)
+        rc = _cabi.lib().pa_swap_blocks_ex(src.data_ptr(), dst.data_ptr(), block_bytes, srcs, dsts, n, kind, engine,
+                                           torch.cuda.current_stream(dev).cuda_stream)
     _cabi.check(rc)

@@ -9,10 +9,19 @@ namespace pa {
 // ---------------------------------------------------------------------------
 // reshape_and_cache / gather_cached_kv
 //
-// One thread moves one 16-byte vector (x = 16/sizeof(T) consecutive head
-// elements) of one token: in the key cache that vector is contiguous
-// ([.., d/x, off, 0..x)), so it is a single 16-byte access; in the value cache
-// its x elements sit block_size apart ([.., d, off]) and move one by one.
+// One CTA moves a tile of kTile consecutive tokens x one head through shared
+// memory.  Rows (key[t][h][:], value[t][h][:]) are contiguous D*sizeof(E) bytes
+// and move as 16-byte vectors.  The cache side is where the layout bites:
+//   key   [blk][h][d/x][off][x]   one 16-byte chunk per (token, d/x); chunks of
+//                                 consecutive tokens of a block are adjacent
+//   value [blk][h][d][off]        one element per (token, d); the B tokens of a
+//                                 block share a 2*B-byte row
+// so the lane order of the cache accesses is chosen per tile: when the tile's
+// slots run consecutively (prefill: a prompt fills its blocks in order) lanes
+// walk tokens first and a half-warp touches one whole 32-byte sector / 256-byte
+// key row; when they are scattered (decode: every token in its own block) lanes
+// walk the head dimension first, which touches 4x fewer 128-byte lines per
+// instruction than any other order.
 // ---------------------------------------------------------------------------
 struct ScatterArgs {
   const void* key;      // gather: destination
@@ -22,63 +31,116 @@ struct ScatterArgs {
   const int32_t* slot_mapping;
   int64_t key_stride;   // elements
   int64_t value_stride;
+  int32_t num_tokens;
   int32_t num_heads;
   int32_t head_size;
   int32_t block_size;
   int32_t vec_ok;       // key/value rows are 16-byte aligned
 };
 
+constexpr int kTile = 16;          // tokens per CTA
+constexpr int kTileThreads = 128;
+
 template <typename E, bool kGather>  // E = uint16_t or uint32_t
-__global__ void __launch_bounds__(256) kv_scatter_gather_kernel(const ScatterArgs a) {
+__global__ void __launch_bounds__(kTileThreads) kv_tile_kernel(const ScatterArgs a) {
   constexpr int X = 16 / sizeof(E);
-  const int token = blockIdx.x;
-  const int slot = a.slot_mapping[token];
-  if (slot < 0) return;  // padding token (not produced by the v0.1.0 scheduler)
-  const int64_t blk = slot / a.block_size;
-  const int off = slot % a.block_size;
+  extern __shared__ __align__(16) unsigned char tile_smem[];
+  __shared__ int64_t s_kbase[kTile];   // element offset of (blk, h, chunk 0, off, 0) in the key cache
+  __shared__ int64_t s_vbase[kTile];   // element offset of (blk, h, row 0, off) in the value cache
+  __shared__ int s_valid[kTile];
+  __shared__ int s_runs;
+
   const int D = a.head_size, B = a.block_size, H = a.num_heads;
   const int nch = D / X;
-  const int nvec = H * nch;
+  const int h = blockIdx.y;
+  const int t0 = blockIdx.x * kTile;
+  const int nt = min(kTile, a.num_tokens - t0);
+  const int row_bytes = D * static_cast<int>(sizeof(E)) + 16;   // +16: spreads the rows over the banks
+  unsigned char* ktile = tile_smem;
+  unsigned char* vtile = tile_smem + kTile * row_bytes;
+
+  if (threadIdx.x < kTile) {
+    const int j = threadIdx.x;
+    int slot = -1;
+    if (j < nt) slot = a.slot_mapping[t0 + j];
+    s_valid[j] = slot >= 0;                      // negative slot: padding token (not produced by the v0.1.0 scheduler)
+    const int64_t blk = slot >= 0 ? slot / B : 0;
+    const int off = slot >= 0 ? slot % B : 0;
+    s_kbase[j] = ((blk * H + h) * nch * B + off) * X;
+    s_vbase[j] = (blk * H + h) * static_cast<int64_t>(D) * B + off;
+    // does this token continue the previous token's block?
+    const int prev = __shfl_up_sync(0x0000ffffu, slot, 1);
+    const bool cont = j > 0 && j < nt && slot >= 0 && prev >= 0 && slot == prev + 1 && (slot % B) != 0;
+    const unsigned m = __ballot_sync(0x0000ffffu, cont);
+    if (j == 0) s_runs = __popc(m);
+  }
+  __syncthreads();
+  const bool token_major = s_runs * 2 >= nt;     // at least half of the tile continues a run
 
   E* kc = reinterpret_cast<E*>(a.key_cache);
   E* vc = reinterpret_cast<E*>(a.value_cache);
-  E* krow = reinterpret_cast<E*>(const_cast<void*>(a.key)) + static_cast<int64_t>(token) * a.key_stride;
-  E* vrow = reinterpret_cast<E*>(const_cast<void*>(a.value)) + static_cast<int64_t>(token) * a.value_stride;
+  E* krows = reinterpret_cast<E*>(const_cast<void*>(a.key)) + static_cast<int64_t>(h) * D;
+  E* vrows = reinterpret_cast<E*>(const_cast<void*>(a.value)) + static_cast<int64_t>(h) * D;
 
-  for (int v = blockIdx.y * blockDim.x + threadIdx.x; v < nvec; v += gridDim.y * blockDim.x) {
-    const int h = v / nch;
-    const int c = v - h * nch;
-    // key:   [blk][h][c][off][0..X)
-    E* kdst = kc + (((blk * H + h) * nch + c) * B + off) * X;
-    // value: [blk][h][c*X + j][off]
-    E* vdst = vc + ((blk * H + h) * D + static_cast<int64_t>(c) * X) * B + off;
-    E* ksrc = krow + static_cast<int64_t>(v) * X;
-    E* vsrc = vrow + static_cast<int64_t>(v) * X;
-    if (!kGather) {
-      union { uint4 q; E e[X]; } kk, vv;
-      if (a.vec_ok) {
-        kk.q = *reinterpret_cast<const uint4*>(ksrc);
-        vv.q = *reinterpret_cast<const uint4*>(vsrc);
+  // rows <-> tile (16-byte vectors; element-wise when the rows are not 16-byte aligned)
+  auto rows_pass = [&](bool to_tile) {
+    for (int idx = threadIdx.x; idx < 2 * nt * nch; idx += kTileThreads) {
+      const int which = idx / (nt * nch);                  // 0 key, 1 value
+      const int r = idx - which * nt * nch;
+      const int j = r / nch, c = r - j * nch;
+      if (!s_valid[j]) continue;
+      E* row = (which ? vrows + (t0 + j) * a.value_stride : krows + (t0 + j) * a.key_stride) + c * X;
+      uint4* cell = reinterpret_cast<uint4*>((which ? vtile : ktile) + j * row_bytes + c * 16);
+      if (to_tile) {
+        if (a.vec_ok) {
+          *cell = *reinterpret_cast<const uint4*>(row);
+        } else {
+          E* ce = reinterpret_cast<E*>(cell);
+#pragma unroll
+          for (int e = 0; e < X; ++e) ce[e] = row[e];
+        }
       } else {
+        if (a.vec_ok) {
+          *reinterpret_cast<uint4*>(row) = *cell;
+        } else {
+          const E* ce = reinterpret_cast<const E*>(cell);
 #pragma unroll
-        for (int j = 0; j < X; ++j) { kk.e[j] = ksrc[j]; vv.e[j] = vsrc[j]; }
-      }
-      *reinterpret_cast<uint4*>(kdst) = kk.q;
-#pragma unroll
-      for (int j = 0; j < X; ++j) vdst[static_cast<int64_t>(j) * B] = vv.e[j];
-    } else {
-      union { uint4 q; E e[X]; } kk, vv;
-      kk.q = *reinterpret_cast<const uint4*>(kdst);
-#pragma unroll
-      for (int j = 0; j < X; ++j) vv.e[j] = vdst[static_cast<int64_t>(j) * B];
-      if (a.vec_ok) {
-        *reinterpret_cast<uint4*>(ksrc) = kk.q;
-        *reinterpret_cast<uint4*>(vsrc) = vv.q;
-      } else {
-#pragma unroll
-        for (int j = 0; j < X; ++j) { ksrc[j] = kk.e[j]; vsrc[j] = vv.e[j]; }
+          for (int e = 0; e < X; ++e) row[e] = ce[e];
+        }
       }
     }
+  };
+
+  // tile <-> caches
+  auto cache_pass = [&]() {
+    // key: one 16-byte chunk per (token j, chunk c)
+    for (int idx = threadIdx.x; idx < nt * nch; idx += kTileThreads) {
+      int j, c;
+      if (token_major) { c = idx / nt; j = idx - c * nt; } else { j = idx / nch; c = idx - j * nch; }
+      if (!s_valid[j]) continue;
+      uint4* cell = reinterpret_cast<uint4*>(ktile + j * row_bytes + c * 16);
+      uint4* g = reinterpret_cast<uint4*>(kc + s_kbase[j] + static_cast<int64_t>(c) * B * X);
+      if (kGather) *cell = *g; else *g = *cell;
+    }
+    // value: one element per (token j, row d)
+    for (int idx = threadIdx.x; idx < nt * D; idx += kTileThreads) {
+      int j, d;
+      if (token_major) { d = idx / nt; j = idx - d * nt; } else { j = idx / D; d = idx - j * D; }
+      if (!s_valid[j]) continue;
+      E* cell = reinterpret_cast<E*>(vtile + j * row_bytes) + d;
+      E* g = vc + s_vbase[j] + static_cast<int64_t>(d) * B;
+      if (kGather) *cell = *g; else *g = *cell;
+    }
+  };
+
+  if (!kGather) {
+    rows_pass(true);
+    __syncthreads();
+    cache_pass();
+  } else {
+    cache_pass();
+    __syncthreads();
+    rows_pass(false);
   }
 }
 
@@ -102,22 +164,26 @@ static int scatter_gather(const void* key, const void* value, void* key_cache, v
     return set_error(PA_ERR_INVALID_ARGUMENT, "%s: head_size %d is not a multiple of x=%d", op, head_size, x);
   if ((reinterpret_cast<uintptr_t>(key_cache) | reinterpret_cast<uintptr_t>(value_cache)) & 15u)
     return set_error(PA_ERR_INVALID_ARGUMENT, "%s: caches must be 16-byte aligned", op);
+  if (num_heads > 65535) return set_error(PA_ERR_INVALID_ARGUMENT, "%s: too many heads (%d)", op, num_heads);
 
   ScatterArgs a;
   a.key = key; a.value = value; a.key_cache = key_cache; a.value_cache = value_cache;
   a.slot_mapping = slot_mapping; a.key_stride = key_stride; a.value_stride = value_stride;
-  a.num_heads = num_heads; a.head_size = head_size; a.block_size = block_size;
+  a.num_tokens = num_tokens; a.num_heads = num_heads; a.head_size = head_size; a.block_size = block_size;
   a.vec_ok = ((reinterpret_cast<uintptr_t>(key) | reinterpret_cast<uintptr_t>(value)) % 16 == 0) &&
-             ((key_stride * es) % 16 == 0) && ((value_stride * es) % 16 == 0);
+             ((key_stride * es) % 16 == 0) && ((value_stride * es) % 16 == 0) && ((head_size * es) % 16 == 0);
 
-  const int nvec = num_heads * (head_size / x);
-  const int threads = nvec >= 256 ? 256 : ((nvec + 31) / 32) * 32;
-  // few tokens (decode): spread one token over several CTAs so the grid still fills the GPU
-  int ysplit = (nvec + threads - 1) / threads;
-  if (static_cast<int64_t>(num_tokens) * ysplit > 148 * 32) ysplit = 1;
-  const dim3 grid(num_tokens, ysplit);
-  if (es == 2) kv_scatter_gather_kernel<uint16_t, kGather><<<grid, threads, 0, stream>>>(a);
-  else kv_scatter_gather_kernel<uint32_t, kGather><<<grid, threads, 0, stream>>>(a);
+  const int smem = 2 * kTile * (head_size * es + 16);
+  if (smem > 200 * 1024) return set_error(PA_ERR_INVALID_ARGUMENT, "%s: head_size %d too large", op, head_size);
+  const dim3 grid((num_tokens + kTile - 1) / kTile, num_heads);
+  auto launch = [&](auto kern) -> int {
+    if (smem > 48 * 1024)
+      PA_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    kern<<<grid, kTileThreads, smem, stream>>>(a);
+    return PA_OK;
+  };
+  int rc = es == 2 ? launch(kv_tile_kernel<uint16_t, kGather>) : launch(kv_tile_kernel<uint32_t, kGather>);
+  if (rc != PA_OK) return rc;
   count_launch();
   return check_cuda(cudaGetLastError(), op);
 }
@@ -206,13 +272,63 @@ static int copy_blocks(void* const* key_cache_ptrs, void* const* value_cache_ptr
 }
 
 // ---------------------------------------------------------------------------
-// swap_blocks: DMA (copy engines stay off the SMs, so a swap on a side stream
-// overlaps the model as in vllm/worker/cache_engine.py:101-118); consecutive
-// block runs are merged so a swap of a whole sequence is a handful of copies
-// instead of one per block (reference: one cudaMemcpyAsync per block, :35-46).
+// swap_blocks.  Two engines, chosen per call:
+//   * few contiguous runs (or pageable host memory): the copy engines, one
+//     cudaMemcpyAsync per run of consecutive (src, dst) blocks -- no SM is used
+//     and a whole-sequence swap is a handful of DMAs (the reference issues one
+//     cudaMemcpyAsync per block, cache_kernels.cu:35-46);
+//   * many scattered blocks with pinned host memory (what
+//     vllm/worker/cache_engine.py:88-97 allocates) or GPU->GPU: one gather/scatter
+//     kernel per <= kSwapMaxPairs blocks that reads/writes the host buffer
+//     directly over PCIe (zero-copy through the unified address space); the
+//     block table rides in the kernel parameters.  Per-block DMA setup
+//     (~7 us for a 160 KiB block) is what limits the first engine here.
+// Either way the work is stream-ordered on the caller's (side) stream, so a swap
+// still overlaps the model as in cache_engine.py:101-118.
 // ---------------------------------------------------------------------------
+constexpr int kSwapMaxPairs = 240;
+constexpr int kSwapMinRunsForKernel = 6;
+
+struct SwapTable {
+  int64_t src_off[kSwapMaxPairs];   // byte offsets
+  int64_t dst_off[kSwapMaxPairs];
+  const char* src;
+  char* dst;
+  int64_t block_bytes;
+};
+static_assert(sizeof(SwapTable) <= 4000, "kernel parameter space");
+
+// grid: (segments per block, blocks)
+__global__ void __launch_bounds__(kCopyThreads) swap_blocks_kernel(const __grid_constant__ SwapTable t) {
+  const char* src = t.src + t.src_off[blockIdx.y];
+  char* dst = t.dst + t.dst_off[blockIdx.y];
+  const int64_t seg = static_cast<int64_t>(blockIdx.x) * kCopySegBytes;
+  uint4 v[kCopyUnroll];
+  int64_t o[kCopyUnroll];
+#pragma unroll
+  for (int j = 0; j < kCopyUnroll; ++j) {
+    o[j] = seg + (static_cast<int64_t>(j) * kCopyThreads + threadIdx.x) * 16;
+    if (o[j] < t.block_bytes) v[j] = *reinterpret_cast<const uint4*>(src + o[j]);
+  }
+#pragma unroll
+  for (int j = 0; j < kCopyUnroll; ++j) {
+    if (o[j] < t.block_bytes) *reinterpret_cast<uint4*>(dst + o[j]) = v[j];
+  }
+}
+
+// device-visible alias of a host pointer if it is pinned (mapped), else nullptr
+static void* mapped_host_pointer(const void* p) {
+  cudaPointerAttributes attr;
+  if (cudaPointerGetAttributes(&attr, p) != cudaSuccess) {
+    cudaGetLastError();
+    return nullptr;
+  }
+  if (attr.type == cudaMemoryTypeHost && attr.devicePointer) return attr.devicePointer;
+  return nullptr;
+}
+
 static int swap_blocks(const void* src, void* dst, int64_t block_bytes, const int64_t* src_blocks,
-                       const int64_t* dst_blocks, int64_t num_blocks, int32_t kind,
+                       const int64_t* dst_blocks, int64_t num_blocks, int32_t kind, int32_t engine,
                        cudaStream_t stream) {
   cudaMemcpyKind k;
   switch (kind) {
@@ -225,9 +341,46 @@ static int swap_blocks(const void* src, void* dst, int64_t block_bytes, const in
   if (num_blocks == 0 || block_bytes == 0) return PA_OK;
   if (!src || !dst || !src_blocks || !dst_blocks)
     return set_error(PA_ERR_INVALID_ARGUMENT, "swap_blocks: null pointer");
-  for (int64_t i = 0; i < num_blocks; ++i)
+  int64_t runs = 1;
+  for (int64_t i = 0; i < num_blocks; ++i) {
     if (src_blocks[i] < 0 || dst_blocks[i] < 0)
       return set_error(PA_ERR_INVALID_ARGUMENT, "swap_blocks: negative block number");
+    if (i > 0 && !(src_blocks[i] == src_blocks[i - 1] + 1 && dst_blocks[i] == dst_blocks[i - 1] + 1)) ++runs;
+  }
+
+  // engine: 0 automatic, 1 copy engines, 2 kernel (falls back to 1 when the host side is not pinned)
+  bool use_kernel = engine == 2 || (engine == 0 && runs >= kSwapMinRunsForKernel);
+  const char* ksrc = static_cast<const char*>(src);
+  char* kdst = static_cast<char*>(dst);
+  if (use_kernel && block_bytes % 16 != 0) use_kernel = false;
+  if (use_kernel && kind == PA_COPY_D2H) {
+    kdst = static_cast<char*>(mapped_host_pointer(dst));
+    use_kernel = kdst != nullptr;
+  }
+  if (use_kernel && kind == PA_COPY_H2D) {
+    ksrc = static_cast<const char*>(mapped_host_pointer(src));
+    use_kernel = ksrc != nullptr;
+  }
+  if (use_kernel && ((reinterpret_cast<uintptr_t>(ksrc) | reinterpret_cast<uintptr_t>(kdst)) & 15u)) use_kernel = false;
+
+  if (use_kernel) {
+    const unsigned segs = static_cast<unsigned>((block_bytes + kCopySegBytes - 1) / kCopySegBytes);
+    for (int64_t p0 = 0; p0 < num_blocks; p0 += kSwapMaxPairs) {
+      const int np = static_cast<int>(num_blocks - p0 < kSwapMaxPairs ? num_blocks - p0 : kSwapMaxPairs);
+      SwapTable t;
+      for (int p = 0; p < np; ++p) {
+        t.src_off[p] = src_blocks[p0 + p] * block_bytes;
+        t.dst_off[p] = dst_blocks[p0 + p] * block_bytes;
+      }
+      t.src = ksrc; t.dst = kdst; t.block_bytes = block_bytes;
+      swap_blocks_kernel<<<dim3(segs, np), kCopyThreads, 0, stream>>>(t);
+      count_launch();
+      const int rc = check_cuda(cudaGetLastError(), "swap_blocks");
+      if (rc != PA_OK) return rc;
+    }
+    return PA_OK;
+  }
+
   int64_t i = 0;
   while (i < num_blocks) {
     int64_t j = i + 1;
@@ -273,7 +426,13 @@ int pa_copy_blocks(void* const* key_cache_ptrs, void* const* value_cache_ptrs, i
 
 int pa_swap_blocks(const void* src, void* dst, int64_t block_bytes, const int64_t* src_blocks,
                    const int64_t* dst_blocks, int64_t num_blocks, int32_t kind, void* stream) {
-  return pa::swap_blocks(src, dst, block_bytes, src_blocks, dst_blocks, num_blocks, kind,
+  return pa::swap_blocks(src, dst, block_bytes, src_blocks, dst_blocks, num_blocks, kind, 0,
+                         static_cast<cudaStream_t>(stream));
+}
+
+int pa_swap_blocks_ex(const void* src, void* dst, int64_t block_bytes, const int64_t* src_blocks,
+                      const int64_t* dst_blocks, int64_t num_blocks, int32_t kind, int32_t engine, void* stream) {
+  return pa::swap_blocks(src, dst, block_bytes, src_blocks, dst_blocks, num_blocks, kind, engine,
                          static_cast<cudaStream_t>(stream));
 }
 
