@@ -107,7 +107,30 @@ def test_operator_signatures_match_the_reference():
     assert sig(cache_ops.swap_blocks) == ["src", "dst", "block_mapping"]
 
 
-def test_no_cpu_fallback():
+@pytest.fixture(params=["torch", "ctypes"])
+def binding(request):
+    """Both routes to the C ABI: the compiled operator binding (lib/pa_torch_ops.so) and plain ctypes."""
+    _cabi.use_binding(request.param)
+    yield request.param
+    _cabi.use_binding("")
+
+
+def test_compiled_binding_is_built_and_links_the_c_abi():
+    ops = _cabi.torch_ops()
+    assert ops is not None, "lib/pa_torch_ops.so must be built by build()"
+    for name in ("single_query_cached_kv_attention", "reshape_and_cache", "gather_cached_kv", "copy_blocks",
+                 "swap_blocks"):
+        assert hasattr(ops, name)
+    out = subprocess.run(["ldd", _cabi.TORCH_OPS_PATH], capture_output=True, text=True).stdout
+    assert "libpaged_b200.so" in out
+    syms = subprocess.run(["nm", "-D", "--undefined-only", _cabi.TORCH_OPS_PATH], capture_output=True, text=True).stdout
+    for name in ("pa_decode_attention_ex", "pa_reshape_and_cache", "pa_gather_cached_kv", "pa_copy_blocks",
+                 "pa_swap_blocks_ex"):
+        assert name in syms, f"the binding must forward to {name}"
+    assert "cudaLaunchKernel" not in syms          # no kernel code in the binding
+
+
+def test_no_cpu_fallback(binding):
     """CPU tensors are refused: the product path never computes on the host."""
     kshape, vshape = vllm_b200.kv_cache_shapes(2, 64, 16, torch.float16)
     kc, vc = torch.zeros(4, *kshape, dtype=torch.float16), torch.zeros(4, *vshape, dtype=torch.float16)

@@ -19,7 +19,7 @@ import torch
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 import bench  # noqa: E402
-from tools.sweep import time_calls  # noqa: E402
+from tools.sweep import time_calls, time_gpu_only  # noqa: E402
 from vllm_b200 import attention_ops, cache_ops  # noqa: E402
 
 DEV = torch.device("cuda", 0)
@@ -86,8 +86,11 @@ def main():
             slots = (starts[:, None] + torch.arange(512, device=DEV)[None, :]).flatten().to(torch.int32)
         a = time_calls(lambda: cache_ops.reshape_and_cache(qkv[:, 1], qkv[:, 2], kcs[0], vcs[0], slots), iters=50)
         b = time_calls(lambda: ref_cache.reshape_and_cache(qkv[:, 1], qkv[:, 2], kcs[0], vcs[0], slots), iters=50)
+        ag = time_gpu_only(lambda: cache_ops.reshape_and_cache(qkv[:, 1], qkv[:, 2], kcs[0], vcs[0], slots), iters=50)
+        bg = time_gpu_only(lambda: ref_cache.reshape_and_cache(qkv[:, 1], qkv[:, 2], kcs[0], vcs[0], slots), iters=50)
         rows.append(dict(op="reshape_and_cache", shape=f"{N} tokens x 40 heads x 128", ours_ms=round(a, 4),
-                         reference_kernel_ms=round(b, 4), speedup=round(b / a, 2)))
+                         reference_kernel_ms=round(b, 4), speedup=round(b / a, 2), ours_gpu_only_ms=round(ag, 4),
+                         reference_gpu_only_ms=round(bg, 4), gpu_only_speedup=round(bg / ag, 2)))
         print(json.dumps(rows[-1]), flush=True)
     cpu = torch.empty((NB, H, D, B), dtype=torch.float16).pin_memory()
     perm_s, perm_d = torch.randperm(NB)[:512].tolist(), torch.randperm(NB)[:512].tolist()

@@ -57,6 +57,49 @@ def time_calls(fn, iters=30, warm=5):
     return e0.elapsed_time(e1) / iters
 
 
+def time_gpu_only(fn, iters=30, warm=5):
+    """Device time per call with the host running ahead: a spin kernel holds the stream while all
+    calls are enqueued, so host-side launch cost is hidden and only GPU execution is between the events."""
+    for _ in range(warm):
+        fn()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    torch.cuda._sleep(int(4e6) + iters * 100000)
+    e0.record()
+    for _ in range(iters):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / iters
+
+
+def sweep_splits(names):
+    res = []
+    for name in names:
+        S, H, D, B, L, dt = SHAPES[name]
+        wl = dict(heads=H, head_size=D, block_size=B, seqs=S, ctx=L, dtype=dt)
+        p = bench.make_problem(wl, H, DEV)
+        out = torch.empty(p["q"].shape, dtype=p["dtype"], device=DEV)
+        nbytes = bench.algorithmic_bytes(S, H, D, B, L, p["kc"].element_size())
+        plan = attention_ops.decode_plan(S, H, D, B, L, p["dtype"])
+        for w, st in ((4, 2), (8, 2), (4, 3), (8, 1), (2, 4)):
+            for sp in (0, 1, 2, 3, 4, 6, 8, 12, 16, 24, 32):
+                tun = _cabi.DecodeTuning(2, w, st, sp)
+                fn = lambda: attention_ops.single_query_cached_kv_attention(out, p["q"], p["kc"], p["vc"], p["scale"],
+                                                                            p["tables"], p["lens"], B, L, tuning=tun)
+                try:
+                    ms = time_gpu_only(fn, iters=40)
+                except RuntimeError as e:
+                    continue
+                row = dict(shape=name, warps=w, stages=st, splits=sp, ms=round(ms, 4), gbs=round(nbytes / ms / 1e6, 1),
+                           auto_plan=[plan.variant, plan.num_warps, plan.num_stages, plan.num_splits])
+                res.append(row)
+                print(json.dumps(row), flush=True)
+        del p, out
+        torch.cuda.empty_cache()
+    return res
+
+
 def sweep_decode(names, extra_splits=(0,)):
     res = []
     for name in names:
@@ -118,8 +161,10 @@ def sweep_movers():
             starts = torch.randperm(NB // 32, device=DEV)[:N // 512] * 32 * B
             slots = (starts[:, None] + torch.arange(512, device=DEV)[None, :]).flatten().to(torch.int32)
         ms = time_calls(lambda: cache_ops.reshape_and_cache(qkv[:, 1], qkv[:, 2], kcs[0], vcs[0], slots), iters=50)
+        gms = time_gpu_only(lambda: cache_ops.reshape_and_cache(qkv[:, 1], qkv[:, 2], kcs[0], vcs[0], slots), iters=50)
         nbytes = N * H * D * 2 * 2 * 2
-        row = dict(op="reshape_and_cache", tokens=N, ms=round(ms, 4), gbs=round(nbytes / ms / 1e6, 1))
+        row = dict(op="reshape_and_cache", tokens=N, ms=round(ms, 4), gpu_only_ms=round(gms, 4),
+                   gbs=round(nbytes / gms / 1e6, 1))
         res.append(row)
         print(json.dumps(row), flush=True)
         out = torch.empty_like(qkv)
@@ -147,7 +192,12 @@ def sweep_movers():
 if __name__ == "__main__":
     what = sys.argv[1] if len(sys.argv) > 1 else "decode"
     os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
-    if what == "decode":
+    if what == "splits":
+        names = sys.argv[2].split(",") if len(sys.argv) > 2 else ["cfg3_g8_h5", "cfg3_g4_h10", "cfg5a_neox_h8_d96",
+                                                                    "cfg5b_opt66_h9", "small_s8_h40", "small_s1_h40"]
+        out = sweep_splits(names)
+        json.dump(out, open(os.path.join(ROOT, "gpurun_out", "sweep_splits.json"), "w"), indent=1)
+    elif what == "decode":
         names = list(SHAPES)
         for a in sys.argv[2:]:
             if a.startswith("--shapes"):

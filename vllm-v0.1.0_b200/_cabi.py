@@ -73,6 +73,39 @@ def lib() -> C.CDLL:
     return _lib
 
 
+TORCH_OPS_PATH = os.path.join(_HERE, "lib", "pa_torch_ops.so")
+_torch_ops = None
+_binding = os.environ.get("PA_BINDING", "")      # "" = compiled binding when built, else ctypes
+
+
+def torch_ops():
+    """The compiled operator binding (csrc/torch_binding.cpp -> lib/pa_torch_ops.so), or None when it is
+    not used.  Both bindings end in the same C ABI; this one unpacks tensors in C++ (~2 us per call)."""
+    global _torch_ops
+    if _binding == "ctypes":
+        return None
+    if _torch_ops is None:
+        if not os.path.exists(TORCH_OPS_PATH):
+            if _binding == "torch":
+                raise RuntimeError(f"{TORCH_OPS_PATH} is missing: build it with `python vllm-v0.1.0_b200/build.py`")
+            return None
+        import importlib.util
+        lib()                                       # libpaged_b200.so first: fails loudly if it is missing
+        spec = importlib.util.spec_from_file_location("pa_torch_ops", TORCH_OPS_PATH)
+        mod = importlib.util.module_from_spec(spec)
+        spec.loader.exec_module(mod)
+        _torch_ops = mod
+    return _torch_ops
+
+
+def use_binding(name: str) -> None:
+    """"torch", "ctypes" or "" (automatic).  Tests run both."""
+    global _binding
+    if name not in ("", "torch", "ctypes"):
+        raise ValueError(name)
+    _binding = name
+
+
 def last_error() -> str:
     return lib().pa_last_error().decode("utf-8", "replace")
 

@@ -50,6 +50,16 @@ def single_query_cached_kv_attention(
     `tuning` (keyword-only, not part of the reference signature) forces a launch
     shape; tests and the tuning sweep use it.
     """
+    ops = _cabi.torch_ops()
+    if ops is not None:
+        if tuning is None:
+            ops.single_query_cached_kv_attention(out, query, key_cache, value_cache, scale, block_tables, context_lens,
+                                                 block_size, max_context_len)
+        else:
+            ops.single_query_cached_kv_attention(out, query, key_cache, value_cache, scale, block_tables, context_lens,
+                                                 block_size, max_context_len, tuning.variant, tuning.num_warps,
+                                                 tuning.num_stages, tuning.num_splits)
+        return
     dev = query.device
     for name, t in (("out", out), ("query", query), ("key_cache", key_cache), ("value_cache", value_cache),
                     ("block_tables", block_tables), ("context_lens", context_lens)):

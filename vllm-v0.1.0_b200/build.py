@@ -67,6 +67,38 @@ def _compile(nvcc: str, src: str, verbose: bool) -> str:
     return obj
 
 
+TORCH_OPS = os.path.join(LIBDIR, "pa_torch_ops.so")
+
+
+def build_torch_binding(force: bool = False) -> str:
+    """lib/pa_torch_ops.so: csrc/torch_binding.cpp (pybind11, torch::Tensor& signatures of the
+    reference) compiled with the host C++ compiler and linked against libpaged_b200.so."""
+    import sysconfig
+    import torch
+    from torch.utils import cpp_extension as ce
+    src = os.path.join(CSRC, "torch_binding.cpp")
+    stamp = TORCH_OPS + ".sha"
+    want = _digest([src, HEADERS[2]]) + torch.__version__
+    if not force and os.path.exists(TORCH_OPS) and os.path.exists(stamp) and open(stamp).read() == want:
+        return TORCH_OPS
+    cxx = "/usr/bin/g++" if os.path.exists("/usr/bin/g++") else (shutil.which("g++") or "g++")
+    tlib = os.path.join(os.path.dirname(torch.__file__), "lib")
+    cmd = [cxx, "-O2", "-std=c++17", "-fPIC", "-shared", "-w", "-fvisibility=hidden",
+           f"-D_GLIBCXX_USE_CXX11_ABI={int(torch._C._GLIBCXX_USE_CXX11_ABI)}", "-DTORCH_API_INCLUDE_EXTENSION_H",
+           "-DTORCH_EXTENSION_NAME=pa_torch_ops", "-I", os.path.join(ROOT, "include"),
+           "-I", sysconfig.get_paths()["include"]]
+    for inc in ce.include_paths("cuda"):
+        cmd += ["-isystem", inc]
+    cmd += [src, "-o", TORCH_OPS, "-L", LIBDIR, "-lpaged_b200", "-Wl,-rpath,$ORIGIN",
+            "-L", tlib, "-lc10", "-lc10_cuda", "-ltorch_cpu", "-ltorch", "-ltorch_python", f"-Wl,-rpath,{tlib}"]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    if r.returncode != 0:
+        raise RuntimeError(f"torch binding failed to build:\n{r.stderr[-4000:]}")
+    with open(stamp, "w") as f:
+        f.write(want)
+    return TORCH_OPS
+
+
 def build(force: bool = False, verbose: bool = False) -> str:
     nvcc = find_nvcc()
     os.makedirs(BUILD, exist_ok=True)
@@ -83,6 +115,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
         r = subprocess.run(cmd, capture_output=True, text=True)
         if r.returncode != 0:
             raise RuntimeError(f"link failed:\n{r.stdout}\n{r.stderr}")
+    build_torch_binding(force)
     return LIB
 
 

@@ -48,6 +48,9 @@ def _kv_rows(op: str, key: torch.Tensor, value: torch.Tensor, key_cache: torch.T
 def reshape_and_cache(key: torch.Tensor, value: torch.Tensor, key_cache: torch.Tensor, value_cache: torch.Tensor,
                       slot_mapping: torch.Tensor) -> None:
     """Scatter the new tokens' key/value rows into the paged caches at slot_mapping."""
+    ops = _cabi.torch_ops()
+    if ops is not None:
+        return ops.reshape_and_cache(key, value, key_cache, value_cache, slot_mapping)
     dev, code, n, h, d, b = _kv_rows("reshape_and_cache", key, value, key_cache, value_cache, slot_mapping)
     with torch.cuda.device(dev):
         rc = _cabi.lib().pa_reshape_and_cache(
@@ -59,6 +62,9 @@ def reshape_and_cache(key: torch.Tensor, value: torch.Tensor, key_cache: torch.T
 def gather_cached_kv(key: torch.Tensor, value: torch.Tensor, key_cache: torch.Tensor, value_cache: torch.Tensor,
                      slot_mapping: torch.Tensor) -> None:
     """Inverse of reshape_and_cache: key/value rows <- caches at slot_mapping."""
+    ops = _cabi.torch_ops()
+    if ops is not None:
+        return ops.gather_cached_kv(key, value, key_cache, value_cache, slot_mapping)
     dev, code, n, h, d, b = _kv_rows("gather_cached_kv", key, value, key_cache, value_cache, slot_mapping)
     with torch.cuda.device(dev):
         rc = _cabi.lib().pa_gather_cached_kv(
@@ -70,6 +76,9 @@ def gather_cached_kv(key: torch.Tensor, value: torch.Tensor, key_cache: torch.Te
 def copy_blocks(key_caches: List[torch.Tensor], value_caches: List[torch.Tensor],
                 block_mapping: Dict[int, List[int]]) -> None:
     """Copy-on-write: block src -> each dst of block_mapping[src], in every layer's key and value cache."""
+    ops = _cabi.torch_ops()
+    if ops is not None:
+        return ops.copy_blocks(key_caches, value_caches, block_mapping)
     num_layers = len(key_caches)
     if num_layers != len(value_caches):
         raise RuntimeError("copy_blocks: key_caches and value_caches differ in length")
@@ -104,6 +113,9 @@ def swap_blocks(src: torch.Tensor, dst: torch.Tensor, block_mapping: Dict[int, i
     """dst[block_mapping[s]] = src[s] for whole cache blocks; GPU<->GPU (same device), GPU->CPU or CPU->GPU.
 
     `engine` (keyword-only, not part of the reference signature): 0 automatic, 1 copy engines, 2 kernel."""
+    ops = _cabi.torch_ops()
+    if ops is not None:
+        return ops.swap_blocks(src, dst, block_mapping, engine)
     if src.is_cuda and dst.is_cuda:
         if src.device != dst.device:
             raise RuntimeError("src and dst must be on the same GPU")
