@@ -90,9 +90,13 @@ def test_plan_is_deterministic_and_sane():
         assert p.variant in (1, 2) and 1 <= p.num_warps <= 8 and 1 <= p.num_stages <= 32 and 1 <= p.num_splits <= 65535
         pages = (ctx + b - 1) // b
         assert p.num_splits <= max(pages, 1)
-    # plenty of (seq, head) items: no split; few items and a long context: split
+    # enough (seq, head) items to occupy the GPU: no split; few items and a long context: split
     assert attention_ops.decode_plan(256, 32, 128, 16, 1024, torch.float16).num_splits == 1
-    assert attention_ops.decode_plan(64, 8, 96, 16, 8192, torch.float16).num_splits > 1
+    assert attention_ops.decode_plan(64, 8, 96, 16, 8192, torch.float16).num_splits == 1
+    assert attention_ops.decode_plan(4, 8, 128, 16, 8192, torch.float16).num_splits > 1
+    # short contexts run as small CTAs
+    assert attention_ops.decode_plan(256, 32, 128, 16, 64, torch.float16).num_warps == 1
+    assert attention_ops.decode_plan(256, 32, 128, 16, 2048, torch.float16).num_warps == 4
 
 
 def test_operator_signatures_match_the_reference():

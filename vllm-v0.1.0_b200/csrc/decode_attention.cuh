@@ -287,8 +287,16 @@ paged_decode_kernel(const DecodeParams p) {
   int32_t* tbl = reinterpret_cast<int32_t*>(smem + map.tbl);
   float* red = reinterpret_cast<float*>(smem + map.red);
 
-  const int ctx = p.context_lens[seq];
   const int first_page = split * p.pages_per_split;
+  // ---- stage the block-table slice (does not wait for the context length: the row is
+  //      max_blocks_per_seq entries long whatever the context, so both loads fly together)
+  {
+    int avail = p.max_blocks_per_seq - first_page;
+    avail = avail < 0 ? 0 : (avail > p.pages_per_split ? p.pages_per_split : avail);
+    const int32_t* row = p.block_tables + static_cast<int64_t>(seq) * p.max_blocks_per_seq + first_page;
+    for (int i = threadIdx.x; i < avail; i += blockDim.x) tbl[i] = __ldg(row + i);
+  }
+  const int ctx = p.context_lens[seq];
   // never walk past the block-table row or the split schedule, whatever context_lens says
   const int pages_true = ctx > 0 ? (ctx + B - 1) / B : 0;
   const int pages_cap = min(p.max_blocks_per_seq, p.pages_per_split * p.num_splits);
@@ -306,11 +314,7 @@ paged_decode_kernel(const DecodeParams p) {
     return;
   }
 
-  // ---- stage the block-table slice; init barriers ---------------------------
-  {
-    const int32_t* row = p.block_tables + static_cast<int64_t>(seq) * p.max_blocks_per_seq + first_page;
-    for (int i = threadIdx.x; i < npages; i += blockDim.x) tbl[i] = row[i];
-  }
+  // ---- init barriers -----------------------------------------------------------
   const uint32_t bars = smem_addr(smem + map.bars) + warp * p.num_stages * 8;
   const uint32_t ring = smem_addr(smem + map.ring) + warp * p.num_stages * 2 * Gm::kPageBytes;
   if constexpr (kStaged) {

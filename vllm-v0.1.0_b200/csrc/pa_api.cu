@@ -107,6 +107,14 @@ constexpr int kMaxSmem = 227 * 1024;
 constexpr int kMaxPagesPerSplit = 8192;  // block-table slice kept in shared memory (32 KiB)
 
 // Fills the zero fields of `t`.  Returns pages_per_split through the pointer.
+//
+// The rules come from sweeps on B200 (profiles/r1_sweep_*.json):
+//   * two ring stages per warp everywhere: deeper rings only cost resident CTAs;
+//   * warps per CTA follow the pages one (sequence, head) has: a warp wants >= 4 pages,
+//     and short contexts run best as many small CTAs (W = 1: 14 resident CTAs per SM);
+//   * the context is split only when the (sequence, head) items cannot occupy the
+//     resident CTA slots once, and never below 8 pages per warp: every extra CTA
+//     costs ~2.7 us of prologue/epilogue during which its slot loads nothing.
 static int make_plan(int num_seqs, int num_heads, int head_size, int block_size, int max_context_len,
                      int dtype, pa_decode_tuning* t, int* pages_per_split) {
   const int page = head_size * block_size * dtype_size(dtype);
@@ -116,15 +124,11 @@ static int make_plan(int num_seqs, int num_heads, int head_size, int block_size,
   if (t->variant <= 0) t->variant = 2;
   const bool staged = t->variant == 2;
   if (t->num_warps <= 0) {
-    t->num_warps = 4;
+    t->num_warps = max_pages <= 4 ? 1 : (max_pages <= 8 ? 2 : 4);
     while (staged && t->num_warps > 1 && t->num_warps * 2 * stage > 160 * 1024) t->num_warps >>= 1;
   }
   if (t->num_warps > 8) t->num_warps = 8;
-  if (t->num_stages <= 0) {
-    // ~64 KiB of ring per CTA: three CTAs per SM, >= 128 KiB of loads in flight per SM
-    int s = (64 * 1024) / (t->num_warps * stage);
-    t->num_stages = s < 2 ? 2 : (s > 8 ? 8 : s);
-  }
+  if (t->num_stages <= 0) t->num_stages = 2;
   if (!staged) t->num_stages = 1;
   if (t->num_stages > 32) t->num_stages = 32;
 
@@ -133,11 +137,12 @@ static int make_plan(int num_seqs, int num_heads, int head_size, int block_size,
     int resident = kMaxSmem / (smem1 + 1024);
     const int by_threads = 2048 / (t->num_warps * kWarp);
     if (resident > by_threads) resident = by_threads;
+    if (resident > 32) resident = 32;
     if (resident < 1) resident = 1;
     const int64_t items = static_cast<int64_t>(num_seqs) * num_heads;
-    const int64_t want = static_cast<int64_t>(sm_count()) * resident * 8;  // ~8 CTAs per resident slot
-    int64_t ns = items > 0 ? (want + items - 1) / items : 1;
-    const int64_t cap = max_pages / (4 * t->num_warps);  // keep >= 4 pages per warp
+    const int64_t slots = static_cast<int64_t>(sm_count()) * resident;
+    int64_t ns = items > 0 ? slots / items : 1;                  // fill the slots once, no more
+    const int64_t cap = max_pages / (8 * t->num_warps);          // keep >= 8 pages per warp
     if (ns > cap) ns = cap;
     if (ns < 1) ns = 1;
     t->num_splits = static_cast<int>(ns);
