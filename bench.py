@@ -243,10 +243,22 @@ def make_host_sample(wl, nseq, seed=0):
     return q, kc, vc, tables, lens
 
 
+def use_all_host_threads():
+    """The CPU legs use every host core this process may run on (torchrun exports OMP_NUM_THREADS=1)."""
+    import torch
+    try:
+        n = len(os.sched_getaffinity(0))
+    except AttributeError:
+        n = os.cpu_count() or 1
+    torch.set_num_threads(max(1, n))
+    return torch.get_num_threads()
+
+
 def time_cpu_reference(wl, nseq, steps=1, warmup=0):
     """seconds per pass of the PyTorch loop oracle over `nseq` sequences (all heads, full context)."""
     import torch
     from oracle import paged_oracle
+    use_all_host_threads()
     q, kc, vc, tables, lens = make_host_sample(wl, nseq)
     out = torch.empty_like(q)
     for _ in range(warmup):
