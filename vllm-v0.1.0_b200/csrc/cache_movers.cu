@@ -36,6 +36,7 @@ struct ScatterArgs {
   int32_t head_size;
   int32_t block_size;
   int32_t vec_ok;       // key/value rows are 16-byte aligned
+  int32_t chunk_shift;  // log2 of the lanes laid along the 16-byte chunks of a row (>= head_size / x)
 };
 
 constexpr int kTile = 16;          // tokens per CTA
@@ -82,15 +83,21 @@ __global__ void __launch_bounds__(kTileThreads) kv_tile_kernel(const ScatterArgs
   E* krows = reinterpret_cast<E*>(const_cast<void*>(a.key)) + static_cast<int64_t>(h) * D;
   E* vrows = reinterpret_cast<E*>(const_cast<void*>(a.value)) + static_cast<int64_t>(h) * D;
 
+  // Thread -> (token, chunk/row) maps are built from shifts and masks only (no integer division
+  // in the loops): cshift = log2(lanes along the 16-byte chunks of a row), dshift likewise for D.
+  const int cshift = a.chunk_shift;
+  const int clanes = 1 << cshift;
+
   // rows <-> tile (16-byte vectors; element-wise when the rows are not 16-byte aligned)
   auto rows_pass = [&](bool to_tile) {
-    for (int idx = threadIdx.x; idx < 2 * nt * nch; idx += kTileThreads) {
-      const int which = idx / (nt * nch);                  // 0 key, 1 value
-      const int r = idx - which * nt * nch;
-      const int j = r / nch, c = r - j * nch;
-      if (!s_valid[j]) continue;
-      E* row = (which ? vrows + (t0 + j) * a.value_stride : krows + (t0 + j) * a.key_stride) + c * X;
-      uint4* cell = reinterpret_cast<uint4*>((which ? vtile : ktile) + j * row_bytes + c * 16);
+    const int c = threadIdx.x & (clanes - 1);
+    if (c >= nch) return;
+    for (int j = threadIdx.x >> cshift; j < 2 * nt; j += kTileThreads >> cshift) {
+      const int which = j >= nt;                           // 0 key, 1 value
+      const int jj = which ? j - nt : j;
+      if (!s_valid[jj]) continue;
+      E* row = (which ? vrows + (t0 + jj) * a.value_stride : krows + (t0 + jj) * a.key_stride) + c * X;
+      uint4* cell = reinterpret_cast<uint4*>((which ? vtile : ktile) + jj * row_bytes + c * 16);
       if (to_tile) {
         if (a.vec_ok) {
           *cell = *reinterpret_cast<const uint4*>(row);
@@ -113,26 +120,75 @@ __global__ void __launch_bounds__(kTileThreads) kv_tile_kernel(const ScatterArgs
 
   // tile <-> caches
   auto cache_pass = [&]() {
-    // key: one 16-byte chunk per (token j, chunk c)
-    for (int idx = threadIdx.x; idx < nt * nch; idx += kTileThreads) {
-      int j, c;
-      if (token_major) { c = idx / nt; j = idx - c * nt; } else { j = idx / nch; c = idx - j * nch; }
-      if (!s_valid[j]) continue;
-      uint4* cell = reinterpret_cast<uint4*>(ktile + j * row_bytes + c * 16);
-      uint4* g = reinterpret_cast<uint4*>(kc + s_kbase[j] + static_cast<int64_t>(c) * B * X);
-      if (kGather) *cell = *g; else *g = *cell;
-    }
-    // value: one element per (token j, row d)
-    for (int idx = threadIdx.x; idx < nt * D; idx += kTileThreads) {
-      int j, d;
-      if (token_major) { d = idx / nt; j = idx - d * nt; } else { j = idx / D; d = idx - j * D; }
-      if (!s_valid[j]) continue;
-      E* cell = reinterpret_cast<E*>(vtile + j * row_bytes) + d;
-      E* g = vc + s_vbase[j] + static_cast<int64_t>(d) * B;
-      if (kGather) *cell = *g; else *g = *cell;
+    if (token_major) {
+      // lanes walk the tile's tokens first: 16 lanes cover one 256-byte key row / one value sector
+      const int j = threadIdx.x & (kTile - 1);
+      if (j < nt && s_valid[j]) {
+        const int64_t kb = s_kbase[j], vb = s_vbase[j];
+        for (int c = threadIdx.x / kTile; c < nch; c += kTileThreads / kTile) {
+          uint4* cell = reinterpret_cast<uint4*>(ktile + j * row_bytes + c * 16);
+          uint4* g = reinterpret_cast<uint4*>(kc + kb + static_cast<int64_t>(c) * B * X);
+          if (kGather) *cell = *g; else *g = *cell;
+        }
+        E* vrow = reinterpret_cast<E*>(vtile + j * row_bytes);
+#pragma unroll 4
+        for (int d = threadIdx.x / kTile; d < D; d += kTileThreads / kTile) {
+          E* g = vc + vb + static_cast<int64_t>(d) * B;
+          if (kGather) vrow[d] = *g; else *g = vrow[d];
+        }
+      }
+    } else {
+      // lanes walk the head dimension first (scattered tokens: fewest 128-byte lines per instruction)
+      const int c = threadIdx.x & (clanes - 1);
+      if (c < nch) {
+        for (int j = threadIdx.x >> cshift; j < nt; j += kTileThreads >> cshift) {
+          if (!s_valid[j]) continue;
+          uint4* cell = reinterpret_cast<uint4*>(ktile + j * row_bytes + c * 16);
+          uint4* g = reinterpret_cast<uint4*>(kc + s_kbase[j] + static_cast<int64_t>(c) * B * X);
+          if (kGather) *cell = *g; else *g = *cell;
+        }
+      }
+      for (int j = 0; j < nt; ++j) {
+        if (!s_valid[j]) continue;
+        E* vrow = reinterpret_cast<E*>(vtile + j * row_bytes);
+        const int64_t vb = s_vbase[j];
+        for (int d = threadIdx.x; d < D; d += kTileThreads) {
+          E* g = vc + vb + static_cast<int64_t>(d) * B;
+          if (kGather) vrow[d] = *g; else *g = vrow[d];
+        }
+      }
     }
   };
 
+  if (!token_major && a.vec_ok && H >= nt) {
+    // Scattered tokens (a decode step: every token is the newest one of its own sequence).  Nothing to
+    // gain from staging, and DRAM locality is per token: one token's K/V destinations are a contiguous
+    // [heads][...] region of its block, 2 bytes (V) or 16 bytes (K) written per 32-byte sector, so the
+    // sector fills dominate and want to stream through one DRAM page.  The tile's H CTAs therefore
+    // regroup: CTA h takes token h % nt and a contiguous share of the heads.
+    const int j = h % nt;
+    if (!s_valid[j]) return;
+    const int m = (H - j + nt - 1) / nt;           // CTAs of this tile that landed on token j
+    const int r = h / nt;
+    const int lo = r * H / m, hi = (r + 1) * H / m;
+    const int64_t hk = static_cast<int64_t>(h) * nch * B * X, hv = static_cast<int64_t>(h) * D * B;
+    E* kdst = kc + (s_kbase[j] - hk);              // head 0 of the token's block
+    E* vdst = vc + (s_vbase[j] - hv);
+    E* krow = krows - static_cast<int64_t>(h) * D + (t0 + j) * a.key_stride;
+    E* vrow = vrows - static_cast<int64_t>(h) * D + (t0 + j) * a.value_stride;
+#pragma unroll 2
+    for (int ci = lo * nch + threadIdx.x; ci < hi * nch; ci += kTileThreads) {
+      uint4* rp = reinterpret_cast<uint4*>(krow + static_cast<int64_t>(ci) * X);
+      uint4* g = reinterpret_cast<uint4*>(kdst + static_cast<int64_t>(ci) * B * X);
+      if (kGather) *rp = *g; else *g = __ldg(rp);
+    }
+#pragma unroll 8
+    for (int i = lo * D + threadIdx.x; i < hi * D; i += kTileThreads) {
+      E* g = vdst + static_cast<int64_t>(i) * B;
+      if (kGather) vrow[i] = *g; else *g = __ldg(vrow + i);
+    }
+    return;
+  }
   if (!kGather) {
     rows_pass(true);
     __syncthreads();
@@ -172,6 +228,10 @@ static int scatter_gather(const void* key, const void* value, void* key_cache, v
   a.num_tokens = num_tokens; a.num_heads = num_heads; a.head_size = head_size; a.block_size = block_size;
   a.vec_ok = ((reinterpret_cast<uintptr_t>(key) | reinterpret_cast<uintptr_t>(value)) % 16 == 0) &&
              ((key_stride * es) % 16 == 0) && ((value_stride * es) % 16 == 0) && ((head_size * es) % 16 == 0);
+
+  a.chunk_shift = 0;
+  while ((1 << a.chunk_shift) < head_size / x) ++a.chunk_shift;
+  if ((1 << a.chunk_shift) > kTileThreads) return set_error(PA_ERR_INVALID_ARGUMENT, "%s: head_size %d too large", op, head_size);
 
   const int smem = 2 * kTile * (head_size * es + 16);
   if (smem > 200 * 1024) return set_error(PA_ERR_INVALID_ARGUMENT, "%s: head_size %d too large", op, head_size);
