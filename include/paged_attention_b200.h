@@ -86,6 +86,14 @@ PA_API uint64_t pa_launch_count(void);
  * Synchronises the device.  Safe to call at any time. */
 PA_API int pa_release_workspaces(void);
 
+/* Measurement aid, not an operator: streams `bytes` of device memory through
+ * shared memory with the decode kernel's TMA bulk-copy pattern (8 KiB chunks,
+ * 4 warps x 2 stages per CTA, ctas_per_sm CTAs per SM; <= 0 -> 3) and no
+ * arithmetic.  Timing it gives the read-bandwidth ceiling of that pattern.
+ * `sink` is a 4-byte device scratch word. */
+PA_API int pa_stream_read_probe(const void* src, int64_t bytes, int32_t ctas_per_sm,
+                         void* sink, void* stream);
+
 /* ------------------------------------------------------------------------ */
 /* decode attention                                                         */
 /* ------------------------------------------------------------------------ */
@@ -192,6 +200,44 @@ PA_API int pa_gather_cached_kv(void* key, void* value, const void* key_cache,
                         int32_t head_size, int32_t block_size,
                         int64_t key_stride, int64_t value_stride,
                         int32_t dtype, void* stream);
+
+/*
+ * replaces: pos_encoding_ops.rotary_embedding_neox
+ *           csrc/pos_encoding.cpp:3-15, csrc/pos_encoding_kernels.cu:5-83
+ *           (the operator that runs immediately before this path:
+ *           vllm/model_executor/layers/attention.py:200-206)
+ *
+ * GPT-NeoX rotary embedding in place on query and key
+ * ([num_tokens][num_heads][head_size], row strides in elements): for i < rot_dim/2
+ *   (x, y) = (row[i], row[rot_dim/2 + i]);  c = cache[pos][i];  s = cache[pos][rot_dim/2 + i]
+ *   row[i] = x*c - y*s;   row[rot_dim/2 + i] = y*c + x*s
+ * positions is int64 [num_tokens]; cos_sin_cache is [max_position][rot_dim] of T.
+ * Every product and sum is rounded to T as the reference does, so results are
+ * bit-identical to the reference's PyTorch implementation of the same formula.
+ */
+PA_API int pa_rotary_embedding_neox(const int64_t* positions, void* query, void* key,
+                             const void* cos_sin_cache, int32_t num_tokens,
+                             int32_t num_heads, int32_t head_size, int32_t rot_dim,
+                             int64_t query_stride, int64_t key_stride,
+                             int32_t dtype, void* stream);
+
+/*
+ * Fusion of the two operators either side of the KV write (one launch, one pass
+ * over k and v): pa_rotary_embedding_neox on tokens [0, num_rope_tokens) followed by
+ * pa_reshape_and_cache of tokens [0, num_cache_tokens) (num_cache_tokens <=
+ * num_rope_tokens: the model pads its token batch, the slot mapping is not
+ * padded).  query and key are left rotated in place exactly as the unfused
+ * sequence leaves them; the caches receive the rotated key and the value.
+ * replaces: vllm/model_executor/layers/attention.py:200-206 + :134-140.
+ */
+PA_API int pa_rope_reshape_and_cache(const int64_t* positions, void* query, void* key,
+                              const void* value, void* key_cache, void* value_cache,
+                              const int32_t* slot_mapping, const void* cos_sin_cache,
+                              int32_t num_rope_tokens, int32_t num_cache_tokens,
+                              int32_t num_heads, int32_t head_size,
+                              int32_t block_size, int32_t rot_dim,
+                              int64_t query_stride, int64_t key_stride,
+                              int64_t value_stride, int32_t dtype, void* stream);
 
 /*
  * replaces: cache_ops.copy_blocks

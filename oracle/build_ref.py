@@ -7,7 +7,7 @@ csrc/cache_kernels.cu are compiled UNMODIFIED, from where they lie under /root/r
 plain nvcc (the reference's setup.py / build system is not run) against the torch headers of
 this image, for compute_100/sm_100 -- the reference itself ships no Blackwell target
 (setup.py:53 falls back to 70..90).  Outputs: oracle/_ref/ref_attention_ops.so and
-oracle/_ref/ref_cache_ops.so (pybind11 modules, git-ignored; they travel to the GPU box with
+oracle/_ref/ref_cache_ops.so, oracle/_ref/ref_pos_encoding_ops.so (pybind11 modules, git-ignored; they travel to the GPU box with
 the snapshot).  No reference source is copied into this repository.
 
 Use: tests/test_gpu_vs_reference_kernels.py compares our kernels with these on the same GPU
@@ -29,6 +29,7 @@ REF = os.environ.get("PA_REFERENCE_ROOT", "/root/reference")
 MODULES = {
     "ref_attention_ops": ["csrc/attention.cpp", "csrc/attention/attention_kernels.cu"],
     "ref_cache_ops": ["csrc/cache.cpp", "csrc/cache_kernels.cu"],
+    "ref_pos_encoding_ops": ["csrc/pos_encoding.cpp", "csrc/pos_encoding_kernels.cu"],
 }
 
 

@@ -40,6 +40,8 @@ def lib() -> C.CDLL:
             fn.argtypes = [vp, vp, vp, vp, vp, i32, i32, i32, i32, i64, i64, i32]
         _lib.po_copy_blocks.restype = None
         _lib.po_copy_blocks.argtypes = [C.POINTER(vp), C.POINTER(vp), i32, C.POINTER(i64), i64, i64]
+        _lib.po_rotary_embedding_neox.restype = None
+        _lib.po_rotary_embedding_neox.argtypes = [vp, vp, vp, vp, i32, i32, i32, i32, i64, i64, i32]
         _lib.po_swap_blocks.restype = None
         _lib.po_swap_blocks.argtypes = [vp, vp, i64, C.POINTER(i64), C.POINTER(i64), i64]
     return _lib
@@ -106,3 +108,14 @@ def swap_blocks(src: torch.Tensor, dst: torch.Tensor, block_mapping: Dict[int, i
     s = (C.c_int64 * max(n, 1))(*keys)
     d = (C.c_int64 * max(n, 1))(*[block_mapping[k] for k in keys])
     lib().po_swap_blocks(src.data_ptr(), dst.data_ptr(), src.element_size() * src[0].numel(), s, d, n)
+
+
+def rotary_embedding_neox(positions: torch.Tensor, query: torch.Tensor, key: torch.Tensor, head_size: int,
+                          cos_sin_cache: torch.Tensor) -> None:
+    _cpu(positions, query, key, cos_sin_cache)
+    assert positions.dtype == torch.int64 and positions.is_contiguous() and cos_sin_cache.is_contiguous()
+    n = query.shape[0]
+    heads = query.shape[1] // head_size if query.dim() == 2 else query.shape[1]
+    lib().po_rotary_embedding_neox(positions.data_ptr(), query.data_ptr(), key.data_ptr(), cos_sin_cache.data_ptr(), n,
+                                   heads, head_size, cos_sin_cache.shape[1], query.stride(0), key.stride(0),
+                                   _DT[query.dtype])

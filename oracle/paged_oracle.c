@@ -242,3 +242,37 @@ void po_swap_blocks(const void* src, void* dst, int64_t block_bytes, const int64
   for (int64_t i = 0; i < num_blocks; ++i)
     memcpy((char*)dst + dst_blocks[i] * block_bytes, (const char*)src + src_blocks[i] * block_bytes, (size_t)block_bytes);
 }
+
+/* GPT-NeoX rotary embedding in place (csrc/pos_encoding_kernels.cu:5-47).  As in the reference's
+ * c10::Half / c10::BFloat16 / float arithmetic every product and every sum is rounded to T before
+ * it is used again; compiled with -ffp-contract=off so no multiply-add is fused. */
+static inline float round_to(int dtype, float v) {
+  if (dtype == 2) return v;
+  return dtype == 0 ? half_to_float(float_to_half(v)) : bf16_to_float(float_to_bf16(v));
+}
+
+void po_rotary_embedding_neox(const int64_t* positions, void* query, void* key, const void* cos_sin_cache,
+                              int32_t num_tokens, int32_t num_heads, int32_t head_size, int32_t rot_dim,
+                              int64_t query_stride, int64_t key_stride, int32_t dtype) {
+  const int embed = rot_dim / 2;
+#pragma omp parallel for schedule(static)
+  for (int t = 0; t < num_tokens; ++t) {
+    const int64_t pos = positions[t];
+    for (int w = 0; w < 2; ++w) {
+      void* base = w == 0 ? query : key;
+      const int64_t row = (int64_t)t * (w == 0 ? query_stride : key_stride);
+      for (int h = 0; h < num_heads; ++h) {
+        for (int i = 0; i < embed; ++i) {
+          const float c = load_elem(cos_sin_cache, pos * rot_dim + i, dtype);
+          const float s = load_elem(cos_sin_cache, pos * rot_dim + embed + i, dtype);
+          const int64_t ix = row + (int64_t)h * head_size + i, iy = ix + embed;
+          const float x = load_elem(base, ix, dtype), y = load_elem(base, iy, dtype);
+          const float xc = round_to(dtype, x * c), ys = round_to(dtype, y * s);
+          const float yc = round_to(dtype, y * c), xs = round_to(dtype, x * s);
+          store_elem(base, ix, dtype, xc - ys);
+          store_elem(base, iy, dtype, yc + xs);
+        }
+      }
+    }
+  }
+}

@@ -12,6 +12,7 @@ instead):
   gather_cached_kv        tests/kernels/test_cache.py:138-143
   copy_blocks             tests/kernels/test_cache.py:51-56
   swap_blocks             csrc/cache_kernels.cu:32-46 (the reference has no test for it)
+  rotary_embedding_neox   tests/kernels/test_pos_encoding.py:12-77 (RefRotaryEmbeddingNeox)
 
 Parity pinning: tests/golden/make_golden.py runs the reference's functions
 themselves (extracted from /root/reference with `ast`) on seeded inputs and
@@ -154,6 +155,43 @@ def swap_blocks(src: torch.Tensor, dst: torch.Tensor, block_mapping: Dict[int, i
     """csrc/cache_kernels.cu:32-46: dst[d] = src[s], whole blocks, in src order."""
     for s in sorted(block_mapping):
         dst[block_mapping[s]] = src[s].to(dst.device)
+
+
+# ---------------------------------------------------------------------------
+# rotary embedding (the operator next to the path; SURVEY.md section 8f rank 1)
+# ---------------------------------------------------------------------------
+def _rotate_half(x: torch.Tensor) -> torch.Tensor:
+    """tests/kernels/test_pos_encoding.py:12-16."""
+    half = x.shape[-1] // 2
+    return torch.cat((-x[..., half:], x[..., :half]), dim=-1)
+
+
+@torch.inference_mode()
+def rotary_embedding_neox(positions: torch.Tensor, query: torch.Tensor, key: torch.Tensor, head_size: int,
+                          cos_sin_cache: torch.Tensor) -> None:
+    """GPT-NeoX rotary embedding in place on query / key ([N, H*D] or [N, H, D], possibly row-strided), in the
+    tensors' own dtype: q*cos + rotate_half(q)*sin on the first rot_dim elements of every head
+    (tests/kernels/test_pos_encoding.py:19-77 RefRotaryEmbeddingNeox; cos/sin rows come from the
+    [max_position, rot_dim] cache the operator is given, csrc/pos_encoding_kernels.cu:19-36)."""
+    n = query.shape[0]
+    rot = cos_sin_cache.shape[1]
+    pos = positions.long()
+    cos = cos_sin_cache[pos, : rot // 2]
+    sin = cos_sin_cache[pos, rot // 2:]
+    cos = torch.cat((cos, cos), dim=-1).unsqueeze(1)          # [N, 1, rot]
+    sin = torch.cat((sin, sin), dim=-1).unsqueeze(1)
+    for t in (query, key):
+        v = t.view(n, -1, head_size) if t.dim() == 2 else t
+        part = v[..., :rot]
+        part.copy_((part * cos) + (_rotate_half(part) * sin))
+
+
+def rope_cos_sin_cache(rot_dim: int, max_position: int, dtype: torch.dtype, base: int = 10000) -> torch.Tensor:
+    """[max_position, rot_dim] table as vllm/model_executor/layers/attention.py:172-186 builds it."""
+    inv_freq = 1.0 / (base ** (torch.arange(0, rot_dim, 2) / rot_dim))
+    t = torch.arange(max_position).float()
+    freqs = torch.einsum("i,j -> ij", t, inv_freq.float())
+    return torch.cat((freqs.cos(), freqs.sin()), dim=-1).to(dtype)
 
 
 # ---------------------------------------------------------------------------

@@ -99,6 +99,26 @@ def cache_case(case_id: str) -> Dict[str, object]:
     }
 
 
+def rope_case_ids() -> List[str]:
+    # dtype x (head_size, rotary_dim): the reference test's head sizes (test_pos_encoding.py:138) with full
+    # rotation, plus partial rotation as GPT-NeoX uses it (rotary_pct 0.25: 96 -> 24)
+    shapes = [(32, 32), (64, 64), (80, 80), (96, 96), (128, 128), (160, 160), (192, 192), (256, 256), (96, 24), (128, 64)]
+    return [f"{dt}-d{d}-r{r}" for dt in DTYPES for (d, r) in shapes]
+
+
+def rope_case(case_id: str) -> Dict[str, object]:
+    """Inputs of rotary_embedding_neox: 53 tokens, 5 heads, positions < 2048, q/k sliced out of a fused qkv."""
+    dt, d, r = case_id.split("-")
+    dtype, head_size, rot_dim = DTYPES[dt], int(d[1:]), int(r[1:])
+    seed = int(hashlib.sha256(("rope" + case_id).encode()).hexdigest()[:8], 16)
+    rs = np.random.RandomState(seed)
+    num_tokens, num_heads, max_position = 53, 5, 2048
+    qkv = _tensor(rs, (num_tokens, 3, num_heads * head_size), dtype, "unit")
+    positions = torch.from_numpy(rs.randint(0, max_position, size=num_tokens).astype(np.int64))
+    return {"dtype": dtype, "head_size": head_size, "rot_dim": rot_dim, "num_heads": num_heads,
+            "max_position": max_position, "qkv": qkv, "positions": positions}
+
+
 def to_numpy(t: torch.Tensor) -> np.ndarray:
     """Bit pattern of a tensor as a numpy array (bf16/f16 -> uint16)."""
     t = t.contiguous()

@@ -12,6 +12,7 @@ source with `ast` and executed unmodified:
                                    ref_single_query_cached_kv_attention (:30-66)
   tests/kernels/test_cache.py      the reference loops inside run_copy_blocks (:51-56),
                                    run_reshape_and_cache (:95-100), run_gather_cached_kv (:138-143)
+  tests/kernels/test_pos_encoding.py  rotate_half, apply_rotary_pos_emb, RefRotaryEmbeddingNeox (:12-77)
 
 Nothing from the reference is copied into this repository: only the outputs of
 those functions on the seeded inputs of cases.py are stored.
@@ -124,7 +125,44 @@ def make_cache() -> None:
     json.dump(meta, open(os.path.join(HERE, "cache_inputs.sha256.json"), "w"), indent=1, sort_keys=True)
 
 
+def make_rope() -> None:
+    """RefRotaryEmbeddingNeox (tests/kernels/test_pos_encoding.py:12-77), run exactly as the reference test
+    runs it (:118-130): module built in fp32, moved to the dtype, called on [N, H, D] views."""
+    import torch.nn as nn
+    import torch.nn.functional as F
+    from typing import Tuple
+    path = os.path.join(REF, "tests/kernels/test_pos_encoding.py")
+    tree = ast.parse(open(path).read())
+    names = {"rotate_half", "apply_rotary_pos_emb", "RefRotaryEmbeddingNeox"}
+    picked = [n for n in tree.body if isinstance(n, (ast.FunctionDef, ast.ClassDef)) and n.name in names]
+    assert len(picked) == 3
+    ns = {"torch": torch, "nn": nn, "F": F, "Tuple": Tuple}
+    exec(compile(ast.Module(body=picked, type_ignores=[]), path, "exec"), ns)
+    import hashlib
+    out, meta = {}, {}
+    for cid in cases.rope_case_ids():
+        c = cases.rope_case(cid)
+        n, h, d = c["qkv"].shape[0], c["num_heads"], c["head_size"]
+        ref = ns["RefRotaryEmbeddingNeox"](dim=c["rot_dim"], max_position_embeddings=c["max_position"]).to(dtype=c["dtype"])
+        with torch.inference_mode():
+            q, k = ref(c["positions"], c["qkv"][:, 0].reshape(n, h, d), c["qkv"][:, 1].reshape(n, h, d))
+        out[f"{cid}/query"] = cases.to_numpy(q.reshape(n, h * d))
+        out[f"{cid}/key"] = cases.to_numpy(k.reshape(n, h * d))
+        meta[cid] = cases.digest(c["qkv"], c["positions"])
+        print(cid, "ok")
+    hashes = {k: hashlib.sha256(v.tobytes()).hexdigest() for k, v in out.items()}
+    small = {k: v for k, v in out.items() if "-d32-" in k}
+    np.savez_compressed(os.path.join(HERE, "rope_golden_small.npz"), **small)
+    json.dump(hashes, open(os.path.join(HERE, "rope_outputs.sha256.json"), "w"), indent=1, sort_keys=True)
+    json.dump(meta, open(os.path.join(HERE, "rope_inputs.sha256.json"), "w"), indent=1, sort_keys=True)
+
+
 if __name__ == "__main__":
     torch.manual_seed(0)
-    make_attention()
-    make_cache()
+    which = sys.argv[1:] or ["attention", "cache", "rope"]
+    if "attention" in which:
+        make_attention()
+    if "cache" in which:
+        make_cache()
+    if "rope" in which:
+        make_rope()

@@ -5,8 +5,8 @@ call libpaged_b200.so (hand-written sm_100a CUDA) through its C ABI.
 Import as `vllm_b200` (the repo-root alias package; this directory's name is
 not a valid Python identifier).
 """
-from . import _cabi, attention_ops, cache_ops  # noqa: F401
+from . import _cabi, attention_ops, cache_ops, pos_encoding_ops  # noqa: F401
 from .cache_engine import CacheEngine, kv_cache_shapes  # noqa: F401
 from . import sharding  # noqa: F401
 
-__all__ = ["attention_ops", "cache_ops", "CacheEngine", "kv_cache_shapes"]
+__all__ = ["attention_ops", "cache_ops", "pos_encoding_ops", "CacheEngine", "kv_cache_shapes"]

@@ -38,6 +38,7 @@ SIGNATURES = {
     "pa_compiled_sm": (C.c_int, []),
     "pa_launch_count": (C.c_uint64, []),
     "pa_release_workspaces": (C.c_int, []),
+    "pa_stream_read_probe": (C.c_int, [_vp, _i64, _i32, _vp, _vp]),
     "pa_decode_attention": (C.c_int, [_vp, _vp, _vp, _vp, _f32, _vp, _vp, _i32, _i32, _i32, _i32, _i32, _i32,
                                       _i64, _i32, _vp]),
     "pa_decode_attention_ex": (C.c_int, [_vp, _vp, _vp, _vp, _f32, _vp, _vp, _i32, _i32, _i32, _i32, _i32, _i32,
@@ -45,6 +46,9 @@ SIGNATURES = {
     "pa_decode_attention_plan": (C.c_int, [_i32, _i32, _i32, _i32, _i32, _i32, C.POINTER(DecodeTuning)]),
     "pa_reshape_and_cache": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _i64, _i64, _i32, _vp]),
     "pa_gather_cached_kv": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _i64, _i64, _i32, _vp]),
+    "pa_rotary_embedding_neox": (C.c_int, [_vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _i64, _i64, _i32, _vp]),
+    "pa_rope_reshape_and_cache": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _i32, _i32,
+                                            _i64, _i64, _i64, _i32, _vp]),
     "pa_copy_blocks": (C.c_int, [C.POINTER(_vp), C.POINTER(_vp), _i32, C.POINTER(_i64), _i64, _i64, _vp]),
     "pa_swap_blocks": (C.c_int, [_vp, _vp, _i64, C.POINTER(_i64), C.POINTER(_i64), _i64, _i32, _vp]),
     "pa_swap_blocks_ex": (C.c_int, [_vp, _vp, _i64, C.POINTER(_i64), C.POINTER(_i64), _i64, _i32, _i32, _vp]),

@@ -2,6 +2,11 @@
 // swap_blocks.  Pure data movement, bit-exact.  Reference behaviour:
 // csrc/cache_kernels.cu:9-47 (swap), :52-138 (copy), :142-224 (reshape_and_cache),
 // :229-386 (gather) of the reference tree.  All offsets are 64-bit.
+#include <cuda_bf16.h>
+#include <cuda_fp16.h>
+
+#include <type_traits>
+
 #include "pa_common.cuh"
 
 namespace pa {
@@ -37,25 +42,71 @@ struct ScatterArgs {
   int32_t block_size;
   int32_t vec_ok;       // key/value rows are 16-byte aligned
   int32_t chunk_shift;  // log2 of the lanes laid along the 16-byte chunks of a row (>= head_size / x)
+  // fused rotary embedding (kRope != 0): q and k rows of tokens [0, num_rope_tokens) are rotated in place
+  const int64_t* positions;   // [num_rope_tokens]
+  void* query;                // [num_rope_tokens][H][D], row stride query_stride
+  const void* cos_sin;        // [max_position][rot_dim]: cos | sin halves
+  int64_t query_stride;
+  int32_t rot_dim;
+  int32_t num_rope_tokens;
+  int32_t rot_shift;          // log2 of the lanes laid along rot_dim / 2
 };
+
+// ---------------------------------------------------------------------------
+// GPT-NeoX rotary embedding of one (x, y) pair, rounded exactly as the reference computes it
+// (csrc/pos_encoding_kernels.cu:36-45 on c10::Half / c10::BFloat16 / float: every product and
+// every sum is formed in fp32 and rounded to T before the next operation, no fused
+// multiply-add), so the result is bit-identical to the reference's PyTorch implementation
+// (tests/kernels/test_pos_encoding.py:12-27, q * cos + rotate_half(q) * sin in dtype T).
+// ---------------------------------------------------------------------------
+template <typename T> struct RopeMath;
+template <> struct RopeMath<F16> {
+  using E = uint16_t;
+  static __device__ __forceinline__ float up(E v) { return __half2float(__ushort_as_half(v)); }
+  static __device__ __forceinline__ E down(float f) { return __half_as_ushort(__float2half_rn(f)); }
+};
+template <> struct RopeMath<BF16> {
+  using E = uint16_t;
+  static __device__ __forceinline__ float up(E v) { return __uint_as_float(static_cast<uint32_t>(v) << 16); }
+  static __device__ __forceinline__ E down(float f) { return __bfloat16_as_ushort(__float2bfloat16_rn(f)); }
+};
+template <> struct RopeMath<F32> {
+  using E = uint32_t;
+  static __device__ __forceinline__ float up(E v) { return __uint_as_float(v); }
+  static __device__ __forceinline__ E down(float f) { return __float_as_uint(f); }
+};
+template <typename T>
+__device__ __forceinline__ void rope_pair(typename RopeMath<T>::E& x, typename RopeMath<T>::E& y,
+                                          typename RopeMath<T>::E c, typename RopeMath<T>::E s) {
+  using M = RopeMath<T>;
+  const float fx = M::up(x), fy = M::up(y), fc = M::up(c), fs = M::up(s);
+  const float xc = M::up(M::down(__fmul_rn(fx, fc))), ys = M::up(M::down(__fmul_rn(fy, fs)));
+  const float yc = M::up(M::down(__fmul_rn(fy, fc))), xs = M::up(M::down(__fmul_rn(fx, fs)));
+  x = M::down(__fsub_rn(xc, ys));
+  y = M::down(__fadd_rn(yc, xs));
+}
+struct NoRope { using E = void; };
 
 constexpr int kTile = 16;          // tokens per CTA
 constexpr int kTileThreads = 128;
 
-template <typename E, bool kGather>  // E = uint16_t or uint32_t
+template <typename E, bool kGather, typename R = NoRope>  // E = uint16_t or uint32_t; R = NoRope or F16/BF16/F32
 __global__ void __launch_bounds__(kTileThreads) kv_tile_kernel(const ScatterArgs a) {
+  constexpr bool kRope = !std::is_same<R, NoRope>::value;
   constexpr int X = 16 / sizeof(E);
   extern __shared__ __align__(16) unsigned char tile_smem[];
   __shared__ int64_t s_kbase[kTile];   // element offset of (blk, h, chunk 0, off, 0) in the key cache
   __shared__ int64_t s_vbase[kTile];   // element offset of (blk, h, row 0, off) in the value cache
-  __shared__ int s_valid[kTile];
+  __shared__ int s_valid[kTile];       // token is written to / read from the caches
+  __shared__ int s_tok[kTile];         // token exists for the rotary embedding (kRope)
+  __shared__ int64_t s_pos[kTile];
   __shared__ int s_runs;
 
   const int D = a.head_size, B = a.block_size, H = a.num_heads;
   const int nch = D / X;
   const int h = blockIdx.y;
   const int t0 = blockIdx.x * kTile;
-  const int nt = min(kTile, a.num_tokens - t0);
+  const int nt = min(kTile, (kRope ? max(a.num_tokens, a.num_rope_tokens) : a.num_tokens) - t0);
   const int row_bytes = D * static_cast<int>(sizeof(E)) + 16;   // +16: spreads the rows over the banks
   unsigned char* ktile = tile_smem;
   unsigned char* vtile = tile_smem + kTile * row_bytes;
@@ -63,7 +114,11 @@ __global__ void __launch_bounds__(kTileThreads) kv_tile_kernel(const ScatterArgs
   if (threadIdx.x < kTile) {
     const int j = threadIdx.x;
     int slot = -1;
-    if (j < nt) slot = a.slot_mapping[t0 + j];
+    if (j < nt && t0 + j < a.num_tokens) slot = a.slot_mapping[t0 + j];
+    if constexpr (kRope) {
+      s_tok[j] = j < nt && t0 + j < a.num_rope_tokens;
+      s_pos[j] = s_tok[j] ? a.positions[t0 + j] : 0;
+    }
     s_valid[j] = slot >= 0;                      // negative slot: padding token (not produced by the v0.1.0 scheduler)
     const int64_t blk = slot >= 0 ? slot / B : 0;
     const int off = slot >= 0 ? slot % B : 0;
@@ -95,7 +150,7 @@ __global__ void __launch_bounds__(kTileThreads) kv_tile_kernel(const ScatterArgs
     for (int j = threadIdx.x >> cshift; j < 2 * nt; j += kTileThreads >> cshift) {
       const int which = j >= nt;                           // 0 key, 1 value
       const int jj = which ? j - nt : j;
-      if (!s_valid[jj]) continue;
+      if (kRope && !which ? !(s_tok[jj] || s_valid[jj]) : !s_valid[jj]) continue;
       E* row = (which ? vrows + (t0 + jj) * a.value_stride : krows + (t0 + jj) * a.key_stride) + c * X;
       uint4* cell = reinterpret_cast<uint4*>((which ? vtile : ktile) + jj * row_bytes + c * 16);
       if (to_tile) {
@@ -160,7 +215,7 @@ __global__ void __launch_bounds__(kTileThreads) kv_tile_kernel(const ScatterArgs
     }
   };
 
-  if (!token_major && a.vec_ok && H >= nt) {
+  if (!kRope && !token_major && a.vec_ok && H >= nt) {
     // Scattered tokens (a decode step: every token is the newest one of its own sequence).  Nothing to
     // gain from staging, and DRAM locality is per token: one token's K/V destinations are a contiguous
     // [heads][...] region of its block, 2 bytes (V) or 16 bytes (K) written per 32-byte sector, so the
@@ -189,7 +244,35 @@ __global__ void __launch_bounds__(kTileThreads) kv_tile_kernel(const ScatterArgs
     }
     return;
   }
-  if (!kGather) {
+  if constexpr (kRope) {
+    // rows -> tile, rotate q (in global memory) and k (in the tile, and back to its row), tile -> caches
+    using M = RopeMath<R>;
+    static_assert(std::is_same<typename M::E, E>::value, "element width");
+    rows_pass(true);
+    __syncthreads();
+    const int embed = a.rot_dim / 2;
+    const int i = threadIdx.x & ((1 << a.rot_shift) - 1);
+    if (i < embed) {
+      const E* cs = reinterpret_cast<const E*>(a.cos_sin);
+      E* qrows = reinterpret_cast<E*>(a.query) + static_cast<int64_t>(h) * D;
+      for (int j = threadIdx.x >> a.rot_shift; j < nt; j += kTileThreads >> a.rot_shift) {
+        if (!s_tok[j]) continue;
+        const E c = __ldg(cs + s_pos[j] * a.rot_dim + i), sn = __ldg(cs + s_pos[j] * a.rot_dim + embed + i);
+        E* kt = reinterpret_cast<E*>(ktile + j * row_bytes);
+        E kx = kt[i], ky = kt[embed + i];
+        rope_pair<R>(kx, ky, c, sn);
+        kt[i] = kx; kt[embed + i] = ky;
+        E* krow = krows + (t0 + j) * a.key_stride;
+        krow[i] = kx; krow[embed + i] = ky;
+        E* qrow = qrows + (t0 + j) * a.query_stride;
+        E qx = qrow[i], qy = qrow[embed + i];
+        rope_pair<R>(qx, qy, c, sn);
+        qrow[i] = qx; qrow[embed + i] = qy;
+      }
+    }
+    __syncthreads();
+    cache_pass();
+  } else if (!kGather) {
     rows_pass(true);
     __syncthreads();
     cache_pass();
@@ -232,6 +315,8 @@ static int scatter_gather(const void* key, const void* value, void* key_cache, v
   a.chunk_shift = 0;
   while ((1 << a.chunk_shift) < head_size / x) ++a.chunk_shift;
   if ((1 << a.chunk_shift) > kTileThreads) return set_error(PA_ERR_INVALID_ARGUMENT, "%s: head_size %d too large", op, head_size);
+  a.positions = nullptr; a.query = nullptr; a.cos_sin = nullptr; a.query_stride = 0;
+  a.rot_dim = 0; a.num_rope_tokens = 0; a.rot_shift = 0;
 
   const int smem = 2 * kTile * (head_size * es + 16);
   if (smem > 200 * 1024) return set_error(PA_ERR_INVALID_ARGUMENT, "%s: head_size %d too large", op, head_size);
@@ -243,6 +328,130 @@ static int scatter_gather(const void* key, const void* value, void* key_cache, v
     return PA_OK;
   };
   int rc = es == 2 ? launch(kv_tile_kernel<uint16_t, kGather>) : launch(kv_tile_kernel<uint32_t, kGather>);
+  if (rc != PA_OK) return rc;
+  count_launch();
+  return check_cuda(cudaGetLastError(), op);
+}
+
+// ---------------------------------------------------------------------------
+// rotary_embedding_neox (stand-alone) and rotary embedding fused with reshape_and_cache
+// ---------------------------------------------------------------------------
+struct RopeArgs {
+  const int64_t* positions;
+  void* query;
+  void* key;
+  const void* cos_sin;
+  int64_t query_stride, key_stride;
+  int32_t num_heads, head_size, rot_dim, rot_shift;
+};
+
+// grid: one CTA per token; lanes along rot_dim / 2, thread rows along heads.
+template <typename T>
+__global__ void __launch_bounds__(256) rope_kernel(const RopeArgs a) {
+  using M = RopeMath<T>;
+  using E = typename M::E;
+  const int64_t token = blockIdx.x;
+  const int64_t pos = a.positions[token];
+  const int embed = a.rot_dim / 2;
+  const int i = threadIdx.x & ((1 << a.rot_shift) - 1);
+  if (i >= embed) return;
+  const E* cs = reinterpret_cast<const E*>(a.cos_sin) + pos * a.rot_dim;
+  const E c = __ldg(cs + i), sn = __ldg(cs + embed + i);
+  E* q = reinterpret_cast<E*>(a.query) + token * a.query_stride;
+  E* k = reinterpret_cast<E*>(a.key) + token * a.key_stride;
+  for (int hh = threadIdx.x >> a.rot_shift; hh < a.num_heads; hh += blockDim.x >> a.rot_shift) {
+    E* qh = q + static_cast<int64_t>(hh) * a.head_size;
+    E* kh = k + static_cast<int64_t>(hh) * a.head_size;
+    E qx = qh[i], qy = qh[embed + i], kx = kh[i], ky = kh[embed + i];
+    rope_pair<T>(qx, qy, c, sn);
+    rope_pair<T>(kx, ky, c, sn);
+    qh[i] = qx; qh[embed + i] = qy;
+    kh[i] = kx; kh[embed + i] = ky;
+  }
+}
+
+static int rope_checks(const char* op, int32_t num_heads, int32_t head_size, int32_t rot_dim, int32_t dtype, int* shift) {
+  if (dtype != PA_F16 && dtype != PA_BF16 && dtype != PA_F32)
+    return set_error(PA_ERR_UNSUPPORTED_DTYPE, "%s: unsupported dtype %d", op, dtype);
+  if (num_heads <= 0 || head_size <= 0 || rot_dim <= 0 || rot_dim % 2 != 0 || rot_dim > head_size)
+    return set_error(PA_ERR_INVALID_ARGUMENT, "%s: bad sizes (heads %d, head_size %d, rot_dim %d)", op, num_heads,
+                     head_size, rot_dim);
+  int sh = 0;
+  while ((1 << sh) < rot_dim / 2) ++sh;
+  if ((1 << sh) > kTileThreads) return set_error(PA_ERR_INVALID_ARGUMENT, "%s: rot_dim %d too large", op, rot_dim);
+  *shift = sh;
+  return PA_OK;
+}
+
+static int rotary_embedding_neox(const int64_t* positions, void* query, void* key, const void* cos_sin,
+                                 int32_t num_tokens, int32_t num_heads, int32_t head_size, int32_t rot_dim,
+                                 int64_t query_stride, int64_t key_stride, int32_t dtype, cudaStream_t stream) {
+  int shift = 0;
+  int rc = rope_checks("rotary_embedding_neox", num_heads, head_size, rot_dim, dtype, &shift);
+  if (rc != PA_OK) return rc;
+  if (num_tokens < 0) return set_error(PA_ERR_INVALID_ARGUMENT, "rotary_embedding_neox: negative token count");
+  if (num_tokens == 0) return PA_OK;
+  if (!positions || !query || !key || !cos_sin) return set_error(PA_ERR_INVALID_ARGUMENT, "rotary_embedding_neox: null pointer");
+  RopeArgs a;
+  a.positions = positions; a.query = query; a.key = key; a.cos_sin = cos_sin;
+  a.query_stride = query_stride; a.key_stride = key_stride;
+  a.num_heads = num_heads; a.head_size = head_size; a.rot_dim = rot_dim; a.rot_shift = shift;
+  int threads = num_heads << shift;
+  threads = threads > 256 ? 256 : (threads < 32 ? 32 : threads);
+  if (dtype == PA_F16) rope_kernel<F16><<<num_tokens, threads, 0, stream>>>(a);
+  else if (dtype == PA_BF16) rope_kernel<BF16><<<num_tokens, threads, 0, stream>>>(a);
+  else rope_kernel<F32><<<num_tokens, threads, 0, stream>>>(a);
+  count_launch();
+  return check_cuda(cudaGetLastError(), "rotary_embedding_neox");
+}
+
+static int rope_reshape_and_cache(const int64_t* positions, void* query, void* key, const void* value, void* key_cache,
+                                  void* value_cache, const int32_t* slot_mapping, const void* cos_sin,
+                                  int32_t num_rope_tokens, int32_t num_cache_tokens, int32_t num_heads,
+                                  int32_t head_size, int32_t block_size, int32_t rot_dim, int64_t query_stride,
+                                  int64_t key_stride, int64_t value_stride, int32_t dtype, cudaStream_t stream) {
+  const char* op = "rope_reshape_and_cache";
+  int shift = 0;
+  int rc = rope_checks(op, num_heads, head_size, rot_dim, dtype, &shift);
+  if (rc != PA_OK) return rc;
+  if (num_rope_tokens < 0 || num_cache_tokens < 0 || num_cache_tokens > num_rope_tokens || block_size <= 0)
+    return set_error(PA_ERR_INVALID_ARGUMENT, "%s: bad token counts (%d rotated, %d cached) or block size %d", op,
+                     num_rope_tokens, num_cache_tokens, block_size);
+  if (num_rope_tokens == 0) return PA_OK;
+  if (!positions || !query || !key || !cos_sin || (num_cache_tokens > 0 && (!value || !key_cache || !value_cache || !slot_mapping)))
+    return set_error(PA_ERR_INVALID_ARGUMENT, "%s: null pointer", op);
+  const int es = dtype_size(dtype);
+  const int x = 16 / es;
+  if (head_size % x != 0)
+    return set_error(PA_ERR_INVALID_ARGUMENT, "%s: head_size %d is not a multiple of x=%d", op, head_size, x);
+  if ((reinterpret_cast<uintptr_t>(key_cache) | reinterpret_cast<uintptr_t>(value_cache)) & 15u)
+    return set_error(PA_ERR_INVALID_ARGUMENT, "%s: caches must be 16-byte aligned", op);
+  if (num_heads > 65535) return set_error(PA_ERR_INVALID_ARGUMENT, "%s: too many heads (%d)", op, num_heads);
+
+  ScatterArgs a;
+  a.key = key; a.value = value; a.key_cache = key_cache; a.value_cache = value_cache;
+  a.slot_mapping = slot_mapping; a.key_stride = key_stride; a.value_stride = value_stride;
+  a.num_tokens = num_cache_tokens; a.num_heads = num_heads; a.head_size = head_size; a.block_size = block_size;
+  a.vec_ok = ((reinterpret_cast<uintptr_t>(key) | reinterpret_cast<uintptr_t>(value)) % 16 == 0) &&
+             ((key_stride * es) % 16 == 0) && ((value_stride * es) % 16 == 0);
+  a.chunk_shift = 0;
+  while ((1 << a.chunk_shift) < head_size / x) ++a.chunk_shift;
+  if ((1 << a.chunk_shift) > kTileThreads) return set_error(PA_ERR_INVALID_ARGUMENT, "%s: head_size %d too large", op, head_size);
+  a.positions = positions; a.query = query; a.cos_sin = cos_sin; a.query_stride = query_stride;
+  a.rot_dim = rot_dim; a.num_rope_tokens = num_rope_tokens; a.rot_shift = shift;
+
+  const int smem = 2 * kTile * (head_size * es + 16);
+  if (smem > 200 * 1024) return set_error(PA_ERR_INVALID_ARGUMENT, "%s: head_size %d too large", op, head_size);
+  const dim3 grid((num_rope_tokens + kTile - 1) / kTile, num_heads);
+  auto launch = [&](auto kern) -> int {
+    if (smem > 48 * 1024)
+      PA_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    kern<<<grid, kTileThreads, smem, stream>>>(a);
+    return PA_OK;
+  };
+  if (dtype == PA_F16) rc = launch(kv_tile_kernel<uint16_t, false, F16>);
+  else if (dtype == PA_BF16) rc = launch(kv_tile_kernel<uint16_t, false, BF16>);
+  else rc = launch(kv_tile_kernel<uint32_t, false, F32>);
   if (rc != PA_OK) return rc;
   count_launch();
   return check_cuda(cudaGetLastError(), op);
@@ -476,6 +685,23 @@ int pa_gather_cached_kv(void* key, void* value, const void* key_cache, const voi
   return pa::scatter_gather<true>(key, value, const_cast<void*>(key_cache), const_cast<void*>(value_cache),
                                   slot_mapping, num_tokens, num_heads, head_size, block_size, key_stride,
                                   value_stride, dtype, static_cast<cudaStream_t>(stream));
+}
+
+int pa_rotary_embedding_neox(const int64_t* positions, void* query, void* key, const void* cos_sin_cache,
+                             int32_t num_tokens, int32_t num_heads, int32_t head_size, int32_t rot_dim,
+                             int64_t query_stride, int64_t key_stride, int32_t dtype, void* stream) {
+  return pa::rotary_embedding_neox(positions, query, key, cos_sin_cache, num_tokens, num_heads, head_size, rot_dim,
+                                   query_stride, key_stride, dtype, static_cast<cudaStream_t>(stream));
+}
+
+int pa_rope_reshape_and_cache(const int64_t* positions, void* query, void* key, const void* value, void* key_cache,
+                              void* value_cache, const int32_t* slot_mapping, const void* cos_sin_cache,
+                              int32_t num_rope_tokens, int32_t num_cache_tokens, int32_t num_heads,
+                              int32_t head_size, int32_t block_size, int32_t rot_dim, int64_t query_stride,
+                              int64_t key_stride, int64_t value_stride, int32_t dtype, void* stream) {
+  return pa::rope_reshape_and_cache(positions, query, key, value, key_cache, value_cache, slot_mapping, cos_sin_cache,
+                                    num_rope_tokens, num_cache_tokens, num_heads, head_size, block_size, rot_dim,
+                                    query_stride, key_stride, value_stride, dtype, static_cast<cudaStream_t>(stream));
 }
 
 int pa_copy_blocks(void* const* key_cache_ptrs, void* const* value_cache_ptrs, int32_t num_layers,

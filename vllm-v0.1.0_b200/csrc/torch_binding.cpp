@@ -200,6 +200,76 @@ void swap_blocks(torch::Tensor& src, torch::Tensor& dst, const std::map<int64_t,
                           static_cast<int64_t>(srcs.size()), kind, engine, stream_of(dev)));
 }
 
+struct RopeArgs {
+  c10::Device dev;
+  int code;
+  int32_t num_tokens, num_heads, rot_dim;
+};
+
+RopeArgs rope_args(const char* op, const torch::Tensor& positions, const torch::Tensor& query, const torch::Tensor& key,
+                   int head_size, const torch::Tensor& cos_sin_cache) {
+  const c10::Device dev = query.device();
+  require_cuda("positions", positions, dev);
+  require_cuda("query", query, dev);
+  require_cuda("key", key, dev);
+  require_cuda("cos_sin_cache", cos_sin_cache, dev);
+  const int code = dtype_code(query);
+  TORCH_CHECK(key.scalar_type() == query.scalar_type() && cos_sin_cache.scalar_type() == query.scalar_type(),
+              op, ": query, key and cos_sin_cache must share one dtype");
+  TORCH_CHECK(positions.scalar_type() == at::ScalarType::Long, op, ": positions must be int64");
+  TORCH_CHECK(query.dim() == 2 && key.dim() == 2 && cos_sin_cache.dim() == 2 && query.sizes() == key.sizes(),
+              op, ": query and key must be [num_tokens, num_heads * head_size]");
+  TORCH_CHECK(query.stride(1) == 1 && key.stride(1) == 1 && cos_sin_cache.is_contiguous() && positions.is_contiguous(),
+              op, ": rows must be contiguous");
+  TORCH_CHECK(head_size > 0 && query.size(1) % head_size == 0, op, ": hidden size ", query.size(1),
+              " is not a multiple of head_size ", head_size);
+  TORCH_CHECK(positions.numel() >= query.size(0), op, ": positions is shorter than the token count");
+  return RopeArgs{dev, code, static_cast<int32_t>(query.size(0)), static_cast<int32_t>(query.size(1) / head_size),
+                  static_cast<int32_t>(cos_sin_cache.size(1))};
+}
+
+void rotary_embedding_neox(torch::Tensor& positions, torch::Tensor& query, torch::Tensor& key, int head_size,
+                           torch::Tensor& cos_sin_cache) {
+  const RopeArgs r = rope_args("rotary_embedding_neox", positions, query, key, head_size, cos_sin_cache);
+  const c10::cuda::CUDAGuard guard(r.dev);
+  check(pa_rotary_embedding_neox(positions.data_ptr<int64_t>(), query.data_ptr(), key.data_ptr(),
+                                 cos_sin_cache.data_ptr(), r.num_tokens, r.num_heads, head_size, r.rot_dim,
+                                 query.stride(0), key.stride(0), r.code, stream_of(r.dev)));
+}
+
+void rotary_embedding_neox_reshape_and_cache(torch::Tensor& positions, torch::Tensor& query, torch::Tensor& key,
+                                             torch::Tensor& value, torch::Tensor& key_cache,
+                                             torch::Tensor& value_cache, torch::Tensor& slot_mapping, int head_size,
+                                             torch::Tensor& cos_sin_cache) {
+  const char* op = "rotary_embedding_neox_reshape_and_cache";
+  const RopeArgs r = rope_args(op, positions, query, key, head_size, cos_sin_cache);
+  require_cuda("value", value, r.dev);
+  require_cuda("key_cache", key_cache, r.dev);
+  require_cuda("value_cache", value_cache, r.dev);
+  require_cuda("slot_mapping", slot_mapping, r.dev);
+  TORCH_CHECK(value.scalar_type() == query.scalar_type() && key_cache.scalar_type() == query.scalar_type() &&
+                  value_cache.scalar_type() == query.scalar_type(),
+              op, ": value and both caches must have the dtype of query");
+  TORCH_CHECK(slot_mapping.scalar_type() == at::ScalarType::Int && slot_mapping.is_contiguous(),
+              op, ": slot_mapping must be a contiguous int32 tensor");
+  TORCH_CHECK(value.dim() == 2 && value.sizes() == key.sizes() && value.stride(1) == 1,
+              op, ": value must be [num_tokens, num_heads * head_size] with contiguous rows");
+  TORCH_CHECK(key_cache.dim() == 5 && value_cache.dim() == 4 && key_cache.is_contiguous() && value_cache.is_contiguous(),
+              op, ": unexpected cache rank or layout");
+  const int64_t block_size = key_cache.size(3), x = key_cache.size(4);
+  TORCH_CHECK(x == 16 / static_cast<int64_t>(key.element_size()) && key_cache.size(1) == r.num_heads &&
+                  key_cache.size(2) * x == head_size && value_cache.size(1) == r.num_heads &&
+                  value_cache.size(2) == head_size && value_cache.size(3) == block_size,
+              op, ": cache shapes do not match the key/value rows");
+  TORCH_CHECK(slot_mapping.numel() <= r.num_tokens, op, ": slot_mapping is longer than the token batch");
+  const c10::cuda::CUDAGuard guard(r.dev);
+  check(pa_rope_reshape_and_cache(positions.data_ptr<int64_t>(), query.data_ptr(), key.data_ptr(), value.data_ptr(),
+                                  key_cache.data_ptr(), value_cache.data_ptr(), slot_mapping.data_ptr<int>(),
+                                  cos_sin_cache.data_ptr(), r.num_tokens, static_cast<int32_t>(slot_mapping.numel()),
+                                  r.num_heads, head_size, static_cast<int32_t>(block_size), r.rot_dim,
+                                  query.stride(0), key.stride(0), value.stride(0), r.code, stream_of(r.dev)));
+}
+
 }  // namespace
 
 PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
@@ -214,5 +284,8 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
   m.def("copy_blocks", &copy_blocks, "Copy-on-write of cache blocks in every layer");
   m.def("swap_blocks", &swap_blocks, py::arg("src"), py::arg("dst"), py::arg("block_mapping"), py::arg("engine") = 0,
         "Move cache blocks between GPU and host caches");
+  m.def("rotary_embedding_neox", &rotary_embedding_neox, "GPT-NeoX rotary embedding in place on query and key");
+  m.def("rotary_embedding_neox_reshape_and_cache", &rotary_embedding_neox_reshape_and_cache,
+        "rotary_embedding_neox followed by reshape_and_cache, one launch");
   m.def("launch_count", []() { return pa_launch_count(); });
 }
