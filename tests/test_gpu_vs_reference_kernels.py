@@ -151,3 +151,33 @@ def test_swap_blocks_bit_exact_vs_reference_implementation(ref_cache):
         ref_cache.swap_blocks(gpu, d_r, {1: 2, 2: 1, 40: 41})
         cache_ops.swap_blocks(gpu, d_o, {1: 2, 2: 1, 40: 41}, engine=engine)
         assert torch.equal(pt.bits(d_r), pt.bits(d_o)), f"gpu->gpu engine {engine}"
+
+
+@pytest.fixture(scope="module")
+def ref_pos_encoding():
+    return _load("ref_pos_encoding_ops")
+
+
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16, torch.float32])
+@pytest.mark.parametrize("head_size,rot", [(32, 32), (64, 64), (80, 80), (96, 96), (128, 128), (160, 160), (192, 192),
+                                           (256, 256), (96, 24)])
+def test_rotary_embedding_vs_reference_kernel(ref_pos_encoding, dtype, head_size, rot):
+    """The reference test's shape (tests/kernels/test_pos_encoding.py:134-146): 2145 tokens, 5 heads,
+    max_position 8192.  16-bit types: bit-identical (both round every product and sum to T).  fp32: the
+    reference kernel's x*cos - y*sin is contracted into a fused multiply-add by nvcc, ours keeps the two
+    roundings of the PyTorch formula, so the last bit may differ."""
+    from oracle import paged_oracle
+    from vllm_b200 import pos_encoding_ops
+    tokens, heads = 2145, 5
+    g = torch.Generator(device=DEV).manual_seed(head_size)
+    qkv = torch.empty((tokens, 3, heads * head_size), dtype=dtype, device=DEV).normal_(generator=g)
+    pos = torch.randint(0, 8192, (tokens,), generator=g, device=DEV)
+    cache = paged_oracle.rope_cos_sin_cache(rot, 8192, dtype).to(DEV)
+    a, b = qkv.clone(), qkv.clone()
+    ref_pos_encoding.rotary_embedding_neox(pos, a[:, 0], a[:, 1], head_size, cache)
+    pos_encoding_ops.rotary_embedding_neox(pos, b[:, 0], b[:, 1], head_size, cache)
+    if dtype == torch.float32:
+        torch.testing.assert_close(b, a, atol=1e-6, rtol=1e-6)
+        assert torch.allclose(b, a, atol=1e-3, rtol=1e-5)          # the reference test's criterion (:130-131)
+    else:
+        assert torch.equal(pt.bits(a), pt.bits(b))

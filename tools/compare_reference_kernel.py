@@ -92,6 +92,44 @@ def main():
                          reference_kernel_ms=round(b, 4), speedup=round(b / a, 2), ours_gpu_only_ms=round(ag, 4),
                          reference_gpu_only_ms=round(bg, 4), gpu_only_speedup=round(bg / ag, 2)))
         print(json.dumps(rows[-1]), flush=True)
+    # rotary embedding + cache write: the reference runs two kernels (pos_encoding_kernels.cu, cache_kernels.cu),
+    # ours one fused launch
+    try:
+        ref_pos = load("ref_pos_encoding_ops")
+    except Exception:
+        ref_pos = None
+    if ref_pos is not None:
+        from oracle import paged_oracle
+        from vllm_b200 import pos_encoding_ops
+        cs = paged_oracle.rope_cos_sin_cache(D, 8192, torch.float16).to(DEV)
+        for N, label in ((256, "decode step, 256 tokens"), (2560, "prefill, 2560 tokens")):
+            qkv = torch.randn((N, 3, H * D), device=DEV).half()
+            pos = torch.randint(0, 8192, (N,), device=DEV)
+            if N <= 256:
+                slots = (torch.randperm(NB, device=DEV)[:N] * B + torch.randint(0, B, (N,), device=DEV)).to(torch.int32)
+            else:
+                starts = torch.randperm(NB // 32, device=DEV)[:N // 512] * 32 * B
+                slots = (starts[:, None] + torch.arange(512, device=DEV)[None, :]).flatten().to(torch.int32)
+            k3, v3 = qkv[:, 1].view(N, H, D), qkv[:, 2].view(N, H, D)
+
+            def ref_two():
+                ref_pos.rotary_embedding_neox(pos, qkv[:, 0], qkv[:, 1], D, cs)
+                ref_cache.reshape_and_cache(k3, v3, kcs[0], vcs[0], slots)
+
+            def ours_two():
+                pos_encoding_ops.rotary_embedding_neox(pos, qkv[:, 0], qkv[:, 1], D, cs)
+                cache_ops.reshape_and_cache(k3, v3, kcs[0], vcs[0], slots)
+
+            def ours_fused():
+                pos_encoding_ops.rotary_embedding_neox_reshape_and_cache(pos, qkv[:, 0], qkv[:, 1], qkv[:, 2], kcs[0],
+                                                                         vcs[0], slots, D, cs)
+            r = time_gpu_only(ref_two, iters=50)
+            o2 = time_gpu_only(ours_two, iters=50)
+            of = time_gpu_only(ours_fused, iters=50)
+            rows.append(dict(op="rotary_embedding_neox + reshape_and_cache", shape=f"{label} x 40 heads x 128",
+                             reference_two_kernels_gpu_ms=round(r, 4), ours_two_kernels_gpu_ms=round(o2, 4),
+                             ours_fused_gpu_ms=round(of, 4), speedup_fused_vs_reference=round(r / of, 2)))
+            print(json.dumps(rows[-1]), flush=True)
     cpu = torch.empty((NB, H, D, B), dtype=torch.float16).pin_memory()
     perm_s, perm_d = torch.randperm(NB)[:512].tolist(), torch.randperm(NB)[:512].tolist()
     mp = {int(s): int(d) for s, d in zip(perm_s, perm_d)}

@@ -50,6 +50,7 @@ struct ScatterArgs {
   int32_t rot_dim;
   int32_t num_rope_tokens;
   int32_t rot_shift;          // log2 of the lanes laid along rot_dim / 2
+  int32_t rot_vec_shift;      // >= 0: 16-byte path, log2 of the lanes laid along (rot_dim / 2) / x; -1: element-wise
 };
 
 // ---------------------------------------------------------------------------
@@ -84,6 +85,18 @@ __device__ __forceinline__ void rope_pair(typename RopeMath<T>::E& x, typename R
   const float yc = M::up(M::down(__fmul_rn(fy, fc))), xs = M::up(M::down(__fmul_rn(fx, fs)));
   x = M::down(__fsub_rn(xc, ys));
   y = M::down(__fadd_rn(yc, xs));
+}
+// the same on a 16-byte vector of pairs: x and y hold X consecutive elements of the two halves
+template <typename T>
+__device__ __forceinline__ void rope_vec(uint4& x, uint4& y, const uint4& c, const uint4& s) {
+  using E = typename RopeMath<T>::E;
+  constexpr int X = 16 / sizeof(E);
+  union V { uint4 q; E e[X]; };
+  V vx, vy, vc, vs;
+  vx.q = x; vy.q = y; vc.q = c; vs.q = s;
+#pragma unroll
+  for (int i = 0; i < X; ++i) rope_pair<T>(vx.e[i], vy.e[i], vc.e[i], vs.e[i]);
+  x = vx.q; y = vy.q;
 }
 struct NoRope { using E = void; };
 
@@ -251,23 +264,49 @@ __global__ void __launch_bounds__(kTileThreads) kv_tile_kernel(const ScatterArgs
     rows_pass(true);
     __syncthreads();
     const int embed = a.rot_dim / 2;
-    const int i = threadIdx.x & ((1 << a.rot_shift) - 1);
-    if (i < embed) {
-      const E* cs = reinterpret_cast<const E*>(a.cos_sin);
-      E* qrows = reinterpret_cast<E*>(a.query) + static_cast<int64_t>(h) * D;
-      for (int j = threadIdx.x >> a.rot_shift; j < nt; j += kTileThreads >> a.rot_shift) {
-        if (!s_tok[j]) continue;
-        const E c = __ldg(cs + s_pos[j] * a.rot_dim + i), sn = __ldg(cs + s_pos[j] * a.rot_dim + embed + i);
-        E* kt = reinterpret_cast<E*>(ktile + j * row_bytes);
-        E kx = kt[i], ky = kt[embed + i];
-        rope_pair<R>(kx, ky, c, sn);
-        kt[i] = kx; kt[embed + i] = ky;
-        E* krow = krows + (t0 + j) * a.key_stride;
-        krow[i] = kx; krow[embed + i] = ky;
-        E* qrow = qrows + (t0 + j) * a.query_stride;
-        E qx = qrow[i], qy = qrow[embed + i];
-        rope_pair<R>(qx, qy, c, sn);
-        qrow[i] = qx; qrow[embed + i] = qy;
+    const E* cs = reinterpret_cast<const E*>(a.cos_sin);
+    E* qrows = reinterpret_cast<E*>(a.query) + static_cast<int64_t>(h) * D;
+    if (a.rot_vec_shift >= 0) {
+      // 16 bytes of each half per thread: cos/sin, k (tile) and q (global) all move as vectors
+      const int ech = embed / X;
+      const int c = threadIdx.x & ((1 << a.rot_vec_shift) - 1);
+      if (c < ech) {
+        for (int j = threadIdx.x >> a.rot_vec_shift; j < nt; j += kTileThreads >> a.rot_vec_shift) {
+          if (!s_tok[j]) continue;
+          const E* csr = cs + s_pos[j] * a.rot_dim;
+          const uint4 cv = __ldg(reinterpret_cast<const uint4*>(csr) + c);
+          const uint4 sv = __ldg(reinterpret_cast<const uint4*>(csr + embed) + c);
+          uint4* qx = reinterpret_cast<uint4*>(qrows + (t0 + j) * a.query_stride) + c;
+          uint4* qy = qx + ech;
+          uint4 x = *qx, y = *qy;
+          uint4* kx = reinterpret_cast<uint4*>(ktile + j * row_bytes) + c;
+          uint4* ky = kx + ech;
+          uint4 u = *kx, v = *ky;
+          rope_vec<R>(x, y, cv, sv);
+          rope_vec<R>(u, v, cv, sv);
+          *qx = x; *qy = y;
+          *kx = u; *ky = v;
+          uint4* gx = reinterpret_cast<uint4*>(krows + (t0 + j) * a.key_stride) + c;
+          gx[0] = u; gx[ech] = v;
+        }
+      }
+    } else {
+      const int i = threadIdx.x & ((1 << a.rot_shift) - 1);
+      if (i < embed) {
+        for (int j = threadIdx.x >> a.rot_shift; j < nt; j += kTileThreads >> a.rot_shift) {
+          if (!s_tok[j]) continue;
+          const E c = __ldg(cs + s_pos[j] * a.rot_dim + i), sn = __ldg(cs + s_pos[j] * a.rot_dim + embed + i);
+          E* kt = reinterpret_cast<E*>(ktile + j * row_bytes);
+          E kx = kt[i], ky = kt[embed + i];
+          rope_pair<R>(kx, ky, c, sn);
+          kt[i] = kx; kt[embed + i] = ky;
+          E* krow = krows + (t0 + j) * a.key_stride;
+          krow[i] = kx; krow[embed + i] = ky;
+          E* qrow = qrows + (t0 + j) * a.query_stride;
+          E qx = qrow[i], qy = qrow[embed + i];
+          rope_pair<R>(qx, qy, c, sn);
+          qrow[i] = qx; qrow[embed + i] = qy;
+        }
       }
     }
     __syncthreads();
@@ -316,7 +355,7 @@ static int scatter_gather(const void* key, const void* value, void* key_cache, v
   while ((1 << a.chunk_shift) < head_size / x) ++a.chunk_shift;
   if ((1 << a.chunk_shift) > kTileThreads) return set_error(PA_ERR_INVALID_ARGUMENT, "%s: head_size %d too large", op, head_size);
   a.positions = nullptr; a.query = nullptr; a.cos_sin = nullptr; a.query_stride = 0;
-  a.rot_dim = 0; a.num_rope_tokens = 0; a.rot_shift = 0;
+  a.rot_dim = 0; a.num_rope_tokens = 0; a.rot_shift = 0; a.rot_vec_shift = -1;
 
   const int smem = 2 * kTile * (head_size * es + 16);
   if (smem > 200 * 1024) return set_error(PA_ERR_INVALID_ARGUMENT, "%s: head_size %d too large", op, head_size);
@@ -342,7 +381,7 @@ struct RopeArgs {
   void* key;
   const void* cos_sin;
   int64_t query_stride, key_stride;
-  int32_t num_heads, head_size, rot_dim, rot_shift;
+  int32_t num_heads, head_size, rot_dim, rot_shift, rot_vec_shift;
 };
 
 // grid: one CTA per token; lanes along rot_dim / 2, thread rows along heads.
@@ -353,6 +392,27 @@ __global__ void __launch_bounds__(256) rope_kernel(const RopeArgs a) {
   const int64_t token = blockIdx.x;
   const int64_t pos = a.positions[token];
   const int embed = a.rot_dim / 2;
+  if (a.rot_vec_shift >= 0) {
+    constexpr int X = 16 / sizeof(E);
+    const int ech = embed / X;
+    const int c = threadIdx.x & ((1 << a.rot_vec_shift) - 1);
+    if (c >= ech) return;
+    const E* csr = reinterpret_cast<const E*>(a.cos_sin) + pos * a.rot_dim;
+    const uint4 cv = __ldg(reinterpret_cast<const uint4*>(csr) + c);
+    const uint4 sv = __ldg(reinterpret_cast<const uint4*>(csr + embed) + c);
+    E* q = reinterpret_cast<E*>(a.query) + token * a.query_stride;
+    E* k = reinterpret_cast<E*>(a.key) + token * a.key_stride;
+    for (int hh = threadIdx.x >> a.rot_vec_shift; hh < a.num_heads; hh += blockDim.x >> a.rot_vec_shift) {
+      uint4* qx = reinterpret_cast<uint4*>(q + static_cast<int64_t>(hh) * a.head_size) + c;
+      uint4* kx = reinterpret_cast<uint4*>(k + static_cast<int64_t>(hh) * a.head_size) + c;
+      uint4 x = qx[0], y = qx[ech], u = kx[0], v = kx[ech];
+      rope_vec<T>(x, y, cv, sv);
+      rope_vec<T>(u, v, cv, sv);
+      qx[0] = x; qx[ech] = y;
+      kx[0] = u; kx[ech] = v;
+    }
+    return;
+  }
   const int i = threadIdx.x & ((1 << a.rot_shift) - 1);
   if (i >= embed) return;
   const E* cs = reinterpret_cast<const E*>(a.cos_sin) + pos * a.rot_dim;
@@ -368,6 +428,20 @@ __global__ void __launch_bounds__(256) rope_kernel(const RopeArgs a) {
     qh[i] = qx; qh[embed + i] = qy;
     kh[i] = kx; kh[embed + i] = ky;
   }
+}
+
+// 16-byte rotary path: both halves of the rotated part, the cos/sin rows and the q/k rows split into whole,
+// aligned 16-byte vectors.  Returns log2 of the lanes along (rot_dim / 2) / x, or -1 for the element-wise path.
+static int rope_vec_shift(int32_t head_size, int32_t rot_dim, int32_t dtype, const void* query, const void* key,
+                          const void* cos_sin, int64_t query_stride, int64_t key_stride) {
+  const int es = dtype_size(dtype), x = 16 / es;
+  if ((rot_dim / 2) % x != 0 || head_size % x != 0) return -1;
+  if ((reinterpret_cast<uintptr_t>(query) | reinterpret_cast<uintptr_t>(key) | reinterpret_cast<uintptr_t>(cos_sin)) & 15u)
+    return -1;
+  if ((query_stride * es) % 16 != 0 || (key_stride * es) % 16 != 0) return -1;
+  int sh = 0;
+  while ((1 << sh) < (rot_dim / 2) / x) ++sh;
+  return sh;
 }
 
 static int rope_checks(const char* op, int32_t num_heads, int32_t head_size, int32_t rot_dim, int32_t dtype, int* shift) {
@@ -396,7 +470,8 @@ static int rotary_embedding_neox(const int64_t* positions, void* query, void* ke
   a.positions = positions; a.query = query; a.key = key; a.cos_sin = cos_sin;
   a.query_stride = query_stride; a.key_stride = key_stride;
   a.num_heads = num_heads; a.head_size = head_size; a.rot_dim = rot_dim; a.rot_shift = shift;
-  int threads = num_heads << shift;
+  a.rot_vec_shift = rope_vec_shift(head_size, rot_dim, dtype, query, key, cos_sin, query_stride, key_stride);
+  int threads = num_heads << (a.rot_vec_shift >= 0 ? a.rot_vec_shift : shift);
   threads = threads > 256 ? 256 : (threads < 32 ? 32 : threads);
   if (dtype == PA_F16) rope_kernel<F16><<<num_tokens, threads, 0, stream>>>(a);
   else if (dtype == PA_BF16) rope_kernel<BF16><<<num_tokens, threads, 0, stream>>>(a);
@@ -439,6 +514,7 @@ static int rope_reshape_and_cache(const int64_t* positions, void* query, void* k
   if ((1 << a.chunk_shift) > kTileThreads) return set_error(PA_ERR_INVALID_ARGUMENT, "%s: head_size %d too large", op, head_size);
   a.positions = positions; a.query = query; a.cos_sin = cos_sin; a.query_stride = query_stride;
   a.rot_dim = rot_dim; a.num_rope_tokens = num_rope_tokens; a.rot_shift = shift;
+  a.rot_vec_shift = a.vec_ok ? rope_vec_shift(head_size, rot_dim, dtype, query, key, cos_sin, query_stride, key_stride) : -1;
 
   const int smem = 2 * kTile * (head_size * es + 16);
   if (smem > 200 * 1024) return set_error(PA_ERR_INVALID_ARGUMENT, "%s: head_size %d too large", op, head_size);
