@@ -381,6 +381,26 @@ def main():
     ms_e, win_e, h2d, d2h = run_e2e_steps(p, args.steps, args.warmup, barrier)
     ms_e = max_over_ranks(ms_e)
 
+    # read ceiling of the kernel's own access pattern (TMA bulk copies, no arithmetic) over the same K pages
+    probe_gbs = None
+    try:
+        lib = _cabi.lib()
+        sink = torch.zeros(4, dtype=torch.int32, device=dev)
+        nbytes = p["kc"].numel() * esize
+        st = torch.cuda.current_stream().cuda_stream
+        for _ in range(3):
+            _cabi.check(lib.pa_stream_read_probe(p["kc"].data_ptr(), nbytes, 3, sink.data_ptr(), st))
+        pe0, pe1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize()
+        pe0.record()
+        for _ in range(10):
+            _cabi.check(lib.pa_stream_read_probe(p["kc"].data_ptr(), nbytes, 3, sink.data_ptr(), st))
+        pe1.record()
+        torch.cuda.synchronize()
+        probe_gbs = nbytes * 10 / (pe0.elapsed_time(pe1) / 1e3) / 1e9
+    except Exception as e:   # the probe is an aid, never a reason to lose the bench line
+        print(f"[bench] read probe failed: {e}", file=sys.stderr)
+
     total_heads = wl["heads"] if wl["shard"] else wl["heads"] * n_gpus
     seqs_job = wl["seqs"] if wl["shard"] else wl["seqs"] * n_gpus      # sequences the whole job finishes per step
     t_step = ms_k / args.steps / 1e3
@@ -432,7 +452,10 @@ def main():
             "hbm_gbs": bytes_job / t_step / 1e9, "hbm_frac_of_8tbs": achieved / NOMINAL_HBM_GBS,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": traffic_from_profiles(args.workload), "peak_source": peak_src,
-                         "algorithmic_bytes_per_launch": bytes_gpu, "kernel": "pa::paged_decode_kernel"},
+                         "algorithmic_bytes_per_launch": bytes_gpu, "kernel": "pa::paged_decode_kernel",
+                         "read_probe_gbs": probe_gbs,
+                         "read_probe_note": "same TMA bulk-copy pattern with no arithmetic (pa_stream_read_probe): "
+                                            "the practical HBM read ceiling on this GPU, measured in this run"},
             "e2e": {"value": seqs_job / t_e2e, "unit": "seqs/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "ms_per_step": t_e2e * 1e3,
                     "note": "per step: pinned host query + block tables + context lens -> device, operator, output -> "
