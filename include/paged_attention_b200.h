@@ -143,7 +143,8 @@ PA_API int pa_decode_attention(void* out, const void* query, const void* key_cac
 
 /* Launch-shape overrides for tuning and tests; 0 / negative = automatic. */
 typedef struct pa_decode_tuning {
-  int32_t variant;    /* 0 auto, 1 direct global loads, 2 bulk-copy staged  */
+  int32_t variant;    /* 0 auto, 1 direct global loads, 2 bulk-copy staged (sibling groups
+                         served together), 3 bulk-copy staged without sibling groups */
   int32_t num_warps;  /* warps per CTA working on one (seq, head, split)     */
   int32_t num_stages; /* pages in flight per warp (variant 2)                */
   int32_t num_splits; /* context partitions per (seq, head)                  */

@@ -244,7 +244,12 @@ struct DecodeParams {
   int32_t num_splits;
   int32_t num_stages;
   int32_t q_vec_ok;           // q rows are 16-byte aligned
+  int32_t num_seqs;
+  int32_t group_rows;         // kGroup: sibling detection over aligned groups of 4 sequences; 1: off
 };
+
+constexpr int kGroup = 4;          // sequences per sibling group (= warps per CTA in group mode)
+constexpr int kGroupMinShared = 4; // shared full pages needed before a group is processed together
 
 // dynamic shared memory map (bytes), W = warps per CTA:
 //   [0, tbl_bytes)                       int32 block numbers of this split
@@ -257,9 +262,9 @@ struct SmemMap {
   using Gm = Geom<T, D, B>;
   static constexpr int kPbufStride = ((2 * Gm::kPbufBytes + 15) / 16) * 16;
   int tbl, red, pbuf, bars, ring, total;
-  __host__ __device__ SmemMap(int pages_per_split, int warps, int stages, bool staged) {
+  __host__ __device__ SmemMap(int pages_per_split, int warps, int stages, bool staged, int group_rows) {
     int o = 0;
-    tbl = o;  o += ((pages_per_split * 4 + 15) / 16) * 16;
+    tbl = o;  o += ((group_rows * pages_per_split * 4 + 15) / 16) * 16;
     red = o;  o += warps * (D + 2) * 4;  o = ((o + 15) / 16) * 16;
     pbuf = o; o += warps * kPbufStride;
     bars = o; o += staged ? warps * stages * 8 : 0;
@@ -283,18 +288,24 @@ paged_decode_kernel(const DecodeParams p) {
   const int nwarps = blockDim.x / kWarp;
   const int H = p.num_heads;
 
-  const SmemMap<T, D, B> map(p.pages_per_split, nwarps, p.num_stages, kStaged);
-  int32_t* tbl = reinterpret_cast<int32_t*>(smem + map.tbl);
+  const SmemMap<T, D, B> map(p.pages_per_split, nwarps, p.num_stages, kStaged, p.group_rows);
+  int32_t* tbl_all = reinterpret_cast<int32_t*>(smem + map.tbl);
   float* red = reinterpret_cast<float*>(smem + map.red);
 
   const int first_page = split * p.pages_per_split;
   // ---- stage the block-table slice (does not wait for the context length: the row is
-  //      max_blocks_per_seq entries long whatever the context, so both loads fly together)
-  {
-    int avail = p.max_blocks_per_seq - first_page;
-    avail = avail < 0 ? 0 : (avail > p.pages_per_split ? p.pages_per_split : avail);
-    const int32_t* row = p.block_tables + static_cast<int64_t>(seq) * p.max_blocks_per_seq + first_page;
-    for (int i = threadIdx.x; i < avail; i += blockDim.x) tbl[i] = __ldg(row + i);
+  //      max_blocks_per_seq entries long whatever the context, so both loads fly together).
+  //      With sibling detection on, the slices of all sequences of this aligned group are staged.
+  const bool grouping = kStaged && p.group_rows > 1;
+  const int r0 = grouping ? seq - seq % kGroup : seq;                       // first sequence of the group
+  const int nrows = grouping ? min(kGroup, p.num_seqs - r0) : 1;
+  int32_t* tbl = tbl_all + (seq - r0) * p.pages_per_split;                  // this sequence's slice
+  int avail = p.max_blocks_per_seq - first_page;
+  avail = avail < 0 ? 0 : (avail > p.pages_per_split ? p.pages_per_split : avail);
+  for (int r = 0; r < nrows; ++r) {
+    const int32_t* row = p.block_tables + static_cast<int64_t>(r0 + r) * p.max_blocks_per_seq + first_page;
+    int32_t* dst = tbl_all + r * p.pages_per_split;
+    for (int i = threadIdx.x; i < avail; i += blockDim.x) dst[i] = __ldg(row + i);
   }
   const int ctx = p.context_lens[seq];
   // never walk past the block-table row or the split schedule, whatever context_lens says
@@ -326,10 +337,10 @@ paged_decode_kernel(const DecodeParams p) {
 
   // ---- q row -> registers ------------------------------------------------------
   uint4 q[Gm::kCpl];
-  {
+  auto load_q = [&](int row_seq) {
     const int g = lane / Gm::kTl;
     const char* qrow = reinterpret_cast<const char*>(p.q) +
-                       (static_cast<int64_t>(seq) * p.q_stride + static_cast<int64_t>(head) * D) * T::kSize;
+                       (static_cast<int64_t>(row_seq) * p.q_stride + static_cast<int64_t>(head) * D) * T::kSize;
 #pragma unroll
     for (int cc = 0; cc < Gm::kCpl; ++cc) {
       const int c = cc * Gm::kG + g;
@@ -346,7 +357,8 @@ paged_decode_kernel(const DecodeParams p) {
         }
       }
     }
-  }
+  };
+  load_q(seq);
   __syncthreads();  // tbl visible to every warp; barrier inits visible
 
   WarpState<T, D, B> st;
@@ -355,12 +367,285 @@ paged_decode_kernel(const DecodeParams p) {
 #pragma unroll
   for (int i = 0; i < Gm::kNvi; ++i) st.acc[i] = 0.f;
 
-  // pages of this warp: local index warp + n * nwarps, n < n_my
-  const int n_my = npages > warp ? (npages - warp + nwarps - 1) / nwarps : 0;
   const uint32_t pbuf0 = smem_addr(smem + map.pbuf) + warp * SmemMap<T, D, B>::kPbufStride;
   const char* kbase = reinterpret_cast<const char*>(p.k_cache) + static_cast<int64_t>(head) * Gm::kPageBytes;
   const char* vbase = reinterpret_cast<const char*>(p.v_cache) + static_cast<int64_t>(head) * Gm::kPageBytes;
   const int64_t block_bytes = static_cast<int64_t>(H) * Gm::kPageBytes;
+  const float eps = 1e-6f * exp2f(ProbScale<T>::kLog2);  // reference: 1/(sum + 1e-6), attention_kernels.cu:213
+
+  // ---- sibling groups ----------------------------------------------------------------
+  // Sequences of one request (parallel sampling, beam search) sit next to each other in the batch and
+  // share the physical pages of their common prefix.  The CTAs of an aligned group of kGroup sequences
+  // all evaluate the same test on the same staged tables: how many leading pages of this split are the
+  // same block in every sequence and lie wholly inside every context.  If enough are, the first CTA of
+  // the group serves the whole group -- one warp per sequence, every shared page fetched from HBM once
+  // and read by all warps from shared memory -- and the others leave.
+  if constexpr (kStaged && T::kSize == 2 && B % 16 == 0) {
+    bool maybe = grouping && nrows > 1;                                              // cheap reject: first pages differ
+    for (int r = 1; maybe && r < nrows; ++r) maybe = tbl_all[0] == tbl_all[r * p.pages_per_split];
+    if (maybe) {
+      __shared__ int s_shared;
+      __shared__ int s_ctx[kGroup];
+      if (threadIdx.x == 0) s_shared = 0x7fffffff;
+      if (threadIdx.x < nrows) s_ctx[threadIdx.x] = p.context_lens[r0 + threadIdx.x];
+      __syncthreads();
+      int limit = avail;
+      for (int r = 0; r < nrows; ++r) {
+        int full = s_ctx[r] / B - first_page;                                      // pages wholly inside the context
+        full = full < 0 ? 0 : full;
+        limit = limit < full ? limit : full;
+      }
+      int first_diff = limit;
+      for (int i = threadIdx.x; i < limit && i < first_diff; i += blockDim.x) {
+        const int32_t b0 = tbl_all[i];
+        bool same = true;
+        for (int r = 1; r < nrows; ++r) same = same && (tbl_all[r * p.pages_per_split + i] == b0);
+        if (!same) first_diff = i;
+      }
+      atomicMin(&s_shared, first_diff);
+      __syncthreads();
+      const int P = s_shared;                                                      // shared pages of this split
+      if (P >= kGroupMinShared) {
+        if (seq != r0) return;                                                     // the group's first CTA does it all
+        // -------- group mode ------------------------------------------------------------------
+        // Phase 1, shared pages: the warps take them round-robin, each page once for ALL sequences of
+        // the group on the tensor cores: S^T[token][seq] = K[token][:] . Q^T (K straight from its x-packed
+        // page as the A operand), column-wise online softmax, O^T[d][seq] += V^T[d][token] . P^T.
+        // Phase 2, the pages that are a sequence's own: warp w <-> sequence r0 + w, as in the plain path.
+        constexpr int KD = D / 16;            // k-steps of Q.K^T = 16-row tiles of O^T
+        constexpr int TT = B / 16;            // 16-token tiles per page
+        const int S = p.num_stages;
+        const uint32_t full0 = smem_addr(smem + map.bars);                         // stage s of warp w: full0 + 8 (w S + s)
+        const uint32_t ring0 = smem_addr(smem + map.ring);
+        const bool active = warp < nrows;
+        const int my_seq = r0 + (active ? warp : 0);
+        const int my_ctx = s_ctx[active ? warp : 0];
+        const int32_t* my_tbl = tbl_all + (active ? warp : 0) * p.pages_per_split;
+        auto issue_stage = [&](int64_t blk, int stage) {
+          const uint32_t bar = full0 + stage * 8;
+          const uint32_t dst = ring0 + stage * 2 * Gm::kPageBytes;
+          mbar_expect_tx(bar, 2 * Gm::kPageBytes);
+          bulk_g2s(dst, kbase + blk * block_bytes, Gm::kPageBytes, bar);
+          bulk_g2s(dst + Gm::kPageBytes, vbase + blk * block_bytes, Gm::kPageBytes, bar);
+        };
+        const int n1 = P > warp ? (P - warp + nwarps - 1) / nwarps : 0;            // shared pages of this warp
+        if (lane == 0)
+          for (int n = 0; n < S && n < n1; ++n) issue_stage(tbl_all[warp + n * nwarps], warp * S + n);
+
+        // B fragments of Q^T: lane holds seq n = lane / 4, elements d = 16 kk + 2 (lane % 4) + {0, 1} (+ 8)
+        uint32_t qb[KD][2];
+        {
+          const int n = lane >> 2;
+          const uint16_t* qn = reinterpret_cast<const uint16_t*>(p.q) +
+                               (static_cast<int64_t>(r0 + (n < nrows ? n : 0)) * p.q_stride + static_cast<int64_t>(head) * D);
+#pragma unroll
+          for (int kk = 0; kk < KD; ++kk) {
+            const int d = 16 * kk + 2 * (lane & 3);
+            qb[kk][0] = n < nrows ? (static_cast<uint32_t>(qn[d]) | (static_cast<uint32_t>(qn[d + 1]) << 16)) : 0u;
+            qb[kk][1] = n < nrows ? (static_cast<uint32_t>(qn[d + 8]) | (static_cast<uint32_t>(qn[d + 9]) << 16)) : 0u;
+          }
+        }
+        float om[KD][4];                     // O^T: rows d = 16 mt + lane/4 (+8), columns seq 2 (lane%4), +1
+#pragma unroll
+        for (int mt = 0; mt < KD; ++mt) { om[mt][0] = om[mt][1] = om[mt][2] = om[mt][3] = 0.f; }
+        float gm0 = -CUDART_INF_F, gm1 = -CUDART_INF_F, gl0 = 0.f, gl1 = 0.f;      // per column; gl: this lane's share
+        {
+          const int mi = lane >> 3, rr = lane & 7;                                 // ldmatrix: matrix, row
+          int stage2 = 0;
+          uint32_t parity = 0;
+          for (int n = 0; n < n1; ++n) {
+            const int stage = warp * S + stage2;
+            mbar_wait(full0 + stage * 8, parity);
+            const uint32_t kpage = ring0 + stage * 2 * Gm::kPageBytes;
+            const uint32_t vpage = kpage + Gm::kPageBytes;
+#pragma unroll
+            for (int tt = 0; tt < TT; ++tt) {
+              float sc[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+              for (int kk = 0; kk < KD; ++kk) {
+                uint32_t a[4];   // matrices: (chunk 2kk, tokens 0-7), (2kk, 8-15), (2kk+1, 0-7), (2kk+1, 8-15)
+                ldmatrix_x4(a, kpage + (((2 * kk + (mi >> 1)) * B + tt * 16 + (mi & 1) * 8 + rr) * 16));
+                mma16816<T>(sc, a, qb[kk][0], qb[kk][1]);
+              }
+#pragma unroll
+              for (int j = 0; j < 4; ++j) sc[j] *= p.scale_log2;
+              float mx0 = fmaxf(sc[0], sc[2]), mx1 = fmaxf(sc[1], sc[3]);
+#pragma unroll
+              for (int o = 4; o < kWarp; o <<= 1) {
+                mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, o));
+                mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, o));
+              }
+              const float nm0 = fmaxf(gm0, mx0), nm1 = fmaxf(gm1, mx1);
+              if (__any_sync(0xffffffffu, nm0 > gm0 || nm1 > gm1)) {
+                const float al0 = fast_exp2(gm0 - nm0), al1 = fast_exp2(gm1 - nm1);
+                gl0 *= al0; gl1 *= al1;
+#pragma unroll
+                for (int mt = 0; mt < KD; ++mt) { om[mt][0] *= al0; om[mt][2] *= al0; om[mt][1] *= al1; om[mt][3] *= al1; }
+                gm0 = nm0; gm1 = nm1;
+              }
+              const float off0 = ProbScale<T>::kLog2 - gm0, off1 = ProbScale<T>::kLog2 - gm1;
+              const uint32_t plo = pack2<T>(fast_exp2(sc[0] + off0), fast_exp2(sc[1] + off1));   // token lane/4
+              const uint32_t phi = pack2<T>(fast_exp2(sc[2] + off0), fast_exp2(sc[3] + off1));   // token lane/4 + 8
+              gl0 += unpack_lo<T>(plo) + unpack_lo<T>(phi);    // sum what the products will actually use
+              gl1 += unpack_hi<T>(plo) + unpack_hi<T>(phi);
+              const uint32_t b0 = movmatrix_trans(plo), b1 = movmatrix_trans(phi);               // P^T as the B operand
+#pragma unroll
+              for (int mt = 0; mt < KD; ++mt) {
+                uint32_t a[4];   // matrices: (rows 0-7, tokens 0-7), (rows 8-15, 0-7), (rows 0-7, 8-15), (rows 8-15, 8-15)
+                ldmatrix_x4(a, vpage + ((16 * mt + (mi & 1) * 8 + rr) * B + tt * 16 + (mi >> 1) * 8) * 2);
+                mma16816<T>(om[mt], a, b0, b1);
+              }
+            }
+            __syncwarp();
+            if (lane == 0 && n + S < n1) issue_stage(tbl_all[warp + (n + S) * nwarps], stage);
+            if (++stage2 == S) { stage2 = 0; parity ^= 1u; }
+          }
+        }
+#pragma unroll
+        for (int o = 4; o < kWarp; o <<= 1) {
+          gl0 += __shfl_xor_sync(0xffffffffu, gl0, o);
+          gl1 += __shfl_xor_sync(0xffffffffu, gl1, o);
+        }
+        __syncthreads();   // every warp is done with its ring: it is reused to hand the partials over
+        // partials of warp w for sequence n: xfer[(w * kGroup + n) * (D + 2) + d], then m, l
+        float* xfer = reinterpret_cast<float*>(smem + map.ring);
+        {
+          const int n0 = 2 * (lane & 3);
+          if (n0 < kGroup) {
+            float* x0 = xfer + (warp * kGroup + n0) * (D + 2);
+            float* x1 = x0 + (D + 2);
+#pragma unroll
+            for (int mt = 0; mt < KD; ++mt) {
+              const int d = 16 * mt + (lane >> 2);
+              x0[d] = om[mt][0]; x1[d] = om[mt][1]; x0[d + 8] = om[mt][2]; x1[d + 8] = om[mt][3];
+            }
+            if ((lane >> 2) == 0) { x0[D] = gm0; x0[D + 1] = gl0; x1[D] = gm1; x1[D + 1] = gl1; }
+          }
+        }
+        __syncthreads();
+        if (active) {
+          // warp w gathers sequence w: the log-sum-exp merge of the four warps' shared-page partials
+          // becomes its running state (value and sum parked in the lanes the final reduction reads)
+          float mm = -CUDART_INF_F;
+          for (int w = 0; w < nwarps; ++w) mm = fmaxf(mm, xfer[(w * kGroup + warp) * (D + 2) + D]);
+          float ll = 0.f;
+          float wgt[8];
+#pragma unroll
+          for (int w = 0; w < 8; ++w) {
+            wgt[w] = 0.f;
+            if (w < nwarps) {
+              const float mw = xfer[(w * kGroup + warp) * (D + 2) + D];
+              wgt[w] = mw > -CUDART_INF_F ? fast_exp2(mw - mm) : 0.f;
+              ll += xfer[(w * kGroup + warp) * (D + 2) + D + 1] * wgt[w];
+            }
+          }
+          st.m = mm;
+          st.l = lane == 0 ? ll : 0.f;
+#pragma unroll
+          for (int i = 0; i < Gm::kNvi; ++i) {
+            const int d = i * Gm::kRpi + lane / Gm::kVpr;
+            float a = 0.f;
+            if (lane % Gm::kVpr == 0 && (Gm::kVExact || d < D)) {
+#pragma unroll
+              for (int w = 0; w < 8; ++w)
+                if (w < nwarps) a += xfer[(w * kGroup + warp) * (D + 2) + d] * wgt[w];
+            }
+            st.acc[i] = a;
+          }
+          if (warp != 0) load_q(my_seq);
+        }
+        __syncthreads();   // partials consumed: the ring carries pages again
+        // Phase 2: the pages that are this sequence's own, through the warp's own S stages
+        if (active) {
+          const int pages_true_w = my_ctx > 0 ? (my_ctx + B - 1) / B : 0;
+          int npages_w = min(pages_true_w, pages_cap) - first_page;
+          npages_w = npages_w < 0 ? 0 : (npages_w > p.pages_per_split ? p.pages_per_split : npages_w);
+          const int last_local_w = pages_true_w <= pages_cap ? pages_true_w - 1 - first_page : -1;
+          const int tail_w = my_ctx - (pages_true_w - 1) * B;
+          const int n_priv = npages_w - P;
+          uint32_t parbits = 0;                                                    // parity of the warp's stages
+          for (int s2 = 0; s2 < S; ++s2) {
+            const int used = n1 > s2 ? (n1 - s2 + S - 1) / S : 0;                  // phases completed in phase 1
+            parbits |= static_cast<uint32_t>(used & 1) << s2;
+          }
+          if (lane == 0)
+            for (int n = 0; n < S && n < n_priv; ++n) issue_stage(my_tbl[P + n], warp * S + n);
+          for (int n = 0; n < n_priv; ++n) {
+            const int s2 = n % S, stage = warp * S + s2;
+            mbar_wait(full0 + stage * 8, (parbits >> s2) & 1u);
+            parbits ^= 1u << s2;
+            const int local = P + n;
+            const int nvalid = (local == last_local_w) ? tail_w : B;
+            const SmemPage kp{ring0 + stage * 2 * Gm::kPageBytes};
+            const SmemPage vp{kp.addr + Gm::kPageBytes};
+            process_page<T, D, B>(kp, vp, q, st, p.scale_log2, nvalid, pbuf0 + (n & 1) * Gm::kPbufBytes, lane);
+            __syncwarp();
+            if (lane == 0 && n + S < n_priv) issue_stage(my_tbl[P + n + S], stage);
+          }
+          // this warp's result is the whole (sequence, head, split)
+#pragma unroll
+          for (int i = 0; i < Gm::kNvi; ++i) {
+#pragma unroll
+            for (int o = 1; o < Gm::kVpr; o <<= 1) st.acc[i] += __shfl_xor_sync(0xffffffffu, st.acc[i], o);
+          }
+          st.l = warp_sum(st.l);
+          const int64_t item = static_cast<int64_t>(my_seq) * H + head;
+          const bool writer = lane % Gm::kVpr == 0;
+          if (p.num_splits == 1) {
+            const float inv = 1.f / (st.l + eps);
+#pragma unroll
+            for (int i = 0; i < Gm::kNvi; ++i) {
+              const int d = i * Gm::kRpi + lane / Gm::kVpr;
+              if (writer && (Gm::kVExact || d < D)) {
+                const float r = st.acc[i] * inv;
+                if constexpr (T::kSize == 2) reinterpret_cast<uint16_t*>(p.out)[item * D + d] = static_cast<uint16_t>(pack2<T>(r, 0.f));
+                else reinterpret_cast<float*>(p.out)[item * D + d] = r;
+              }
+            }
+          } else {
+            float* part = p.ws_part + (item * p.num_splits + split) * (D + 2);
+#pragma unroll
+            for (int i = 0; i < Gm::kNvi; ++i) {
+              const int d = i * Gm::kRpi + lane / Gm::kVpr;
+              if (writer && (Gm::kVExact || d < D)) __stcg(part + d, st.acc[i]);
+            }
+            if (lane == 0) { __stcg(part + D, st.m); __stcg(part + D + 1, st.l); }
+            __threadfence();
+            __syncwarp();
+            uint32_t prev = 0;
+            if (lane == 0) prev = atomicAdd(p.ws_ticket + item, 1u);
+            prev = __shfl_sync(0xffffffffu, prev, 0);
+            if (prev == static_cast<uint32_t>(p.num_splits) - 1u) {                // last split of this (sequence, head)
+              if (lane == 0) p.ws_ticket[item] = 0u;
+              __threadfence();
+              const float* parts = p.ws_part + item * p.num_splits * (D + 2);
+              float gm = -CUDART_INF_F;
+              for (int s2 = 0; s2 < p.num_splits; ++s2) gm = fmaxf(gm, __ldcg(parts + s2 * (D + 2) + D));
+              float gl = 0.f;
+              for (int s2 = 0; s2 < p.num_splits; ++s2) {
+                const float ms = __ldcg(parts + s2 * (D + 2) + D);
+                if (ms > -CUDART_INF_F) gl += __ldcg(parts + s2 * (D + 2) + D + 1) * fast_exp2(ms - gm);
+              }
+              for (int d = lane; d < D; d += kWarp) {
+                float a = 0.f;
+                for (int s2 = 0; s2 < p.num_splits; ++s2) {
+                  const float ms = __ldcg(parts + s2 * (D + 2) + D);
+                  if (ms > -CUDART_INF_F) a += __ldcg(parts + s2 * (D + 2) + d) * fast_exp2(ms - gm);
+                }
+                const float r = a / (gl + eps);
+                if constexpr (T::kSize == 2) reinterpret_cast<uint16_t*>(p.out)[item * D + d] = static_cast<uint16_t>(pack2<T>(r, 0.f));
+                else reinterpret_cast<float*>(p.out)[item * D + d] = r;
+              }
+            }
+          }
+        }
+        return;
+      }
+    }
+  }
+
+  // pages of this warp: local index warp + n * nwarps, n < n_my
+  const int n_my = npages > warp ? (npages - warp + nwarps - 1) / nwarps : 0;
   // local index of the context's last page and the number of tokens in it
   const int last_local = pages_true <= pages_cap ? pages_true - 1 - first_page : -1;
   const int tail = ctx - (pages_true - 1) * B;
@@ -421,7 +706,6 @@ paged_decode_kernel(const DecodeParams p) {
   }
   __syncthreads();
 
-  const float eps = 1e-6f * exp2f(ProbScale<T>::kLog2);  // reference: 1/(sum + 1e-6), attention_kernels.cu:213
   float cta_m = -CUDART_INF_F;
   for (int w = 0; w < nwarps; ++w) cta_m = fmaxf(cta_m, red[w * (D + 2) + D]);
   float cta_l = 0.f;
@@ -504,7 +788,7 @@ struct DecodeLaunch {
 
 // bytes of dynamic shared memory a launch needs (same formula as the kernel)
 int decode_smem_bytes(int dtype, int head_size, int block_size, int pages_per_split,
-                      int warps, int stages, bool staged);
+                      int warps, int stages, bool staged, int group_rows);
 
 int launch_decode_f16(const DecodeLaunch& l);
 int launch_decode_bf16(const DecodeLaunch& l);
@@ -513,7 +797,7 @@ int launch_decode_f32(const DecodeLaunch& l);
 #ifdef PA_DECODE_IMPL
 template <typename T, int D, int B, bool kStaged>
 static int launch_one(const DecodeLaunch& l) {
-  const SmemMap<T, D, B> map(l.params.pages_per_split, l.num_warps, l.params.num_stages, kStaged);
+  const SmemMap<T, D, B> map(l.params.pages_per_split, l.num_warps, l.params.num_stages, kStaged, l.params.group_rows);
   auto kern = paged_decode_kernel<T, D, B, kStaged>;
   if (map.total > 48 * 1024) {
     PA_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, map.total));

@@ -89,11 +89,19 @@ static int sm_count() {
   return cached[dev];
 }
 
+// sibling-group detection needs one CTA warp per sequence of a group and room for the group's table slices
+static int group_rows_for(bool staged, int variant, int warps, int num_seqs, int pages_per_split, int dtype,
+                          int block_size) {
+  // the group path multiplies on the tensor cores: 16-bit types, pages of whole 16-token tiles
+  return (staged && variant != 3 && warps == kGroup && num_seqs >= 2 && pages_per_split <= 2048 &&
+          dtype != PA_F32 && block_size % 16 == 0) ? kGroup : 1;
+}
+
 int decode_smem_bytes(int dtype, int head_size, int block_size, int pages_per_split, int warps, int stages,
-                      bool staged) {
+                      bool staged, int group_rows) {
   const int page = head_size * block_size * dtype_size(dtype);
   const int pbuf = ((2 * block_size * dtype_size(dtype) + 15) / 16) * 16;
-  int o = ((pages_per_split * 4 + 15) / 16) * 16;
+  int o = ((group_rows * pages_per_split * 4 + 15) / 16) * 16;
   o += warps * (head_size + 2) * 4;
   o = ((o + 15) / 16) * 16;
   o += warps * pbuf;
@@ -122,7 +130,7 @@ static int make_plan(int num_seqs, int num_heads, int head_size, int block_size,
   const int max_pages = max_context_len > 0 ? (max_context_len + block_size - 1) / block_size : 1;
 
   if (t->variant <= 0) t->variant = 2;
-  const bool staged = t->variant == 2;
+  const bool staged = t->variant >= 2;
   if (t->num_warps <= 0) {
     t->num_warps = max_pages <= 4 ? 1 : (max_pages <= 8 ? 2 : 4);
     while (staged && t->num_warps > 1 && t->num_warps * 2 * stage > 160 * 1024) t->num_warps >>= 1;
@@ -133,7 +141,7 @@ static int make_plan(int num_seqs, int num_heads, int head_size, int block_size,
   if (t->num_stages > 32) t->num_stages = 32;
 
   if (t->num_splits <= 0) {
-    const int smem1 = decode_smem_bytes(dtype, head_size, block_size, 64, t->num_warps, t->num_stages, staged);
+    const int smem1 = decode_smem_bytes(dtype, head_size, block_size, 64, t->num_warps, t->num_stages, staged, kGroup);
     int resident = kMaxSmem / (smem1 + 1024);
     const int by_threads = 2048 / (t->num_warps * kWarp);
     if (resident > by_threads) resident = by_threads;
@@ -158,10 +166,11 @@ static int make_plan(int num_seqs, int num_heads, int head_size, int block_size,
   *pages_per_split = pps;
 
   // shrink the ring until the CTA fits
+  const int gr = group_rows_for(staged, t->variant, t->num_warps, num_seqs, pps, dtype, block_size);
   while (staged && t->num_stages > 1 &&
-         decode_smem_bytes(dtype, head_size, block_size, pps, t->num_warps, t->num_stages, true) > kMaxSmem)
+         decode_smem_bytes(dtype, head_size, block_size, pps, t->num_warps, t->num_stages, true, gr) > kMaxSmem)
     --t->num_stages;
-  if (decode_smem_bytes(dtype, head_size, block_size, pps, t->num_warps, t->num_stages, staged) > kMaxSmem)
+  if (decode_smem_bytes(dtype, head_size, block_size, pps, t->num_warps, t->num_stages, staged, gr) > kMaxSmem)
     return set_error(PA_ERR_INVALID_ARGUMENT, "launch shape does not fit shared memory (warps %d, stages %d)",
                      t->num_warps, t->num_stages);
   return PA_OK;
@@ -200,7 +209,7 @@ static int decode(void* out, const void* query, const void* key_cache, const voi
 
   pa_decode_tuning t = {0, 0, 0, 0};
   if (tuning) t = *tuning;
-  if (t.variant < 0 || t.variant > 2) return set_error(PA_ERR_INVALID_ARGUMENT, "invalid variant %d", t.variant);
+  if (t.variant < 0 || t.variant > 3) return set_error(PA_ERR_INVALID_ARGUMENT, "invalid variant %d", t.variant);
   int pps = 0;
   rc = make_plan(num_seqs, num_heads, head_size, block_size, max_context_len, dtype, &t, &pps);
   if (rc != PA_OK) return rc;
@@ -218,6 +227,8 @@ static int decode(void* out, const void* query, const void* key_cache, const voi
   p.num_splits = t.num_splits;
   p.num_stages = t.num_stages;
   p.q_vec_ok = (reinterpret_cast<uintptr_t>(query) % 16 == 0) && ((q_stride * es) % 16 == 0);
+  p.num_seqs = num_seqs;
+  p.group_rows = group_rows_for(t.variant >= 2, t.variant, t.num_warps, num_seqs, pps, dtype, block_size);
   if (t.num_splits > 1) {
     const size_t items = static_cast<size_t>(num_seqs) * num_heads;
     rc = get_workspace(stream, items * sizeof(uint32_t), items * t.num_splits * (head_size + 2) * sizeof(float),
@@ -225,7 +236,7 @@ static int decode(void* out, const void* query, const void* key_cache, const voi
     if (rc != PA_OK) return rc;
   }
   l.num_seqs = num_seqs; l.head_size = head_size; l.block_size = block_size;
-  l.num_warps = t.num_warps; l.staged = (t.variant == 2); l.stream = stream;
+  l.num_warps = t.num_warps; l.staged = (t.variant >= 2); l.stream = stream;
   switch (dtype) {
     case PA_F16:  return launch_decode_f16(l);
     case PA_BF16: return launch_decode_bf16(l);
