@@ -262,9 +262,9 @@ struct SmemMap {
   using Gm = Geom<T, D, B>;
   static constexpr int kPbufStride = ((2 * Gm::kPbufBytes + 15) / 16) * 16;
   int tbl, red, pbuf, bars, ring, total;
-  __host__ __device__ SmemMap(int pages_per_split, int warps, int stages, bool staged, int group_rows) {
+  __host__ __device__ SmemMap(int pages_per_split, int warps, int stages, bool staged) {
     int o = 0;
-    tbl = o;  o += ((group_rows * pages_per_split * 4 + 15) / 16) * 16;
+    tbl = o;  o += ((pages_per_split * 4 + 15) / 16) * 16;
     red = o;  o += warps * (D + 2) * 4;  o = ((o + 15) / 16) * 16;
     pbuf = o; o += warps * kPbufStride;
     bars = o; o += staged ? warps * stages * 8 : 0;
@@ -274,7 +274,7 @@ struct SmemMap {
   }
 };
 
-template <typename T, int D, int B, bool kStaged>
+template <typename T, int D, int B, bool kStaged, bool kGroups = false>
 __global__ void __launch_bounds__(256)
 paged_decode_kernel(const DecodeParams p) {
   using Gm = Geom<T, D, B>;
@@ -288,24 +288,29 @@ paged_decode_kernel(const DecodeParams p) {
   const int nwarps = blockDim.x / kWarp;
   const int H = p.num_heads;
 
-  const SmemMap<T, D, B> map(p.pages_per_split, nwarps, p.num_stages, kStaged, p.group_rows);
-  int32_t* tbl_all = reinterpret_cast<int32_t*>(smem + map.tbl);
+  const SmemMap<T, D, B> map(p.pages_per_split, nwarps, p.num_stages, kStaged);
+  int32_t* tbl = reinterpret_cast<int32_t*>(smem + map.tbl);
   float* red = reinterpret_cast<float*>(smem + map.red);
 
   const int first_page = split * p.pages_per_split;
   // ---- stage the block-table slice (does not wait for the context length: the row is
-  //      max_blocks_per_seq entries long whatever the context, so both loads fly together).
-  //      With sibling detection on, the slices of all sequences of this aligned group are staged.
-  const bool grouping = kStaged && p.group_rows > 1;
-  const int r0 = grouping ? seq - seq % kGroup : seq;                       // first sequence of the group
-  const int nrows = grouping ? min(kGroup, p.num_seqs - r0) : 1;
-  int32_t* tbl = tbl_all + (seq - r0) * p.pages_per_split;                  // this sequence's slice
+  //      max_blocks_per_seq entries long whatever the context, so both loads fly together)
   int avail = p.max_blocks_per_seq - first_page;
   avail = avail < 0 ? 0 : (avail > p.pages_per_split ? p.pages_per_split : avail);
-  for (int r = 0; r < nrows; ++r) {
-    const int32_t* row = p.block_tables + static_cast<int64_t>(r0 + r) * p.max_blocks_per_seq + first_page;
-    int32_t* dst = tbl_all + r * p.pages_per_split;
-    for (int i = threadIdx.x; i < avail; i += blockDim.x) dst[i] = __ldg(row + i);
+  {
+    const int32_t* row = p.block_tables + static_cast<int64_t>(seq) * p.max_blocks_per_seq + first_page;
+    for (int i = threadIdx.x; i < avail; i += blockDim.x) tbl[i] = __ldg(row + i);
+  }
+  // sibling detection (kGroups): first page and context length of every sequence of this aligned group
+  constexpr bool kGroupPath = kGroups && kStaged && T::kSize == 2 && B % 16 == 0;
+  const bool grouping = kGroupPath && p.group_rows > 1;
+  const int r0 = grouping ? seq - seq % kGroup : seq;                       // first sequence of the group
+  const int nrows = grouping ? min(kGroup, p.num_seqs - r0) : 1;
+  __shared__ int s_first[kGroup];
+  __shared__ int s_ctx[kGroup];
+  if (grouping && threadIdx.x < nrows) {
+    s_first[threadIdx.x] = avail > 0 ? __ldg(p.block_tables + static_cast<int64_t>(r0 + threadIdx.x) * p.max_blocks_per_seq + first_page) : -1 - static_cast<int>(threadIdx.x);
+    s_ctx[threadIdx.x] = p.context_lens[r0 + threadIdx.x];
   }
   const int ctx = p.context_lens[seq];
   // never walk past the block-table row or the split schedule, whatever context_lens says
@@ -380,14 +385,12 @@ paged_decode_kernel(const DecodeParams p) {
   // same block in every sequence and lie wholly inside every context.  If enough are, the first CTA of
   // the group serves the whole group -- one warp per sequence, every shared page fetched from HBM once
   // and read by all warps from shared memory -- and the others leave.
-  if constexpr (kStaged && T::kSize == 2 && B % 16 == 0) {
+  if constexpr (kGroupPath) {
     bool maybe = grouping && nrows > 1;                                              // cheap reject: first pages differ
-    for (int r = 1; maybe && r < nrows; ++r) maybe = tbl_all[0] == tbl_all[r * p.pages_per_split];
+    for (int r = 1; maybe && r < nrows; ++r) maybe = s_first[0] == s_first[r];
     if (maybe) {
       __shared__ int s_shared;
-      __shared__ int s_ctx[kGroup];
       if (threadIdx.x == 0) s_shared = 0x7fffffff;
-      if (threadIdx.x < nrows) s_ctx[threadIdx.x] = p.context_lens[r0 + threadIdx.x];
       __syncthreads();
       int limit = avail;
       for (int r = 0; r < nrows; ++r) {
@@ -396,10 +399,12 @@ paged_decode_kernel(const DecodeParams p) {
         limit = limit < full ? limit : full;
       }
       int first_diff = limit;
+      const int32_t* rows0 = p.block_tables + static_cast<int64_t>(r0) * p.max_blocks_per_seq + first_page;
       for (int i = threadIdx.x; i < limit && i < first_diff; i += blockDim.x) {
-        const int32_t b0 = tbl_all[i];
+        const int32_t b0 = tbl[i];
         bool same = true;
-        for (int r = 1; r < nrows; ++r) same = same && (tbl_all[r * p.pages_per_split + i] == b0);
+        for (int r = 0; r < nrows; ++r)
+          if (r0 + r != seq) same = same && (__ldg(rows0 + static_cast<int64_t>(r) * p.max_blocks_per_seq + i) == b0);
         if (!same) first_diff = i;
       }
       atomicMin(&s_shared, first_diff);
@@ -420,7 +425,7 @@ paged_decode_kernel(const DecodeParams p) {
         const bool active = warp < nrows;
         const int my_seq = r0 + (active ? warp : 0);
         const int my_ctx = s_ctx[active ? warp : 0];
-        const int32_t* my_tbl = tbl_all + (active ? warp : 0) * p.pages_per_split;
+        const int32_t* my_row = p.block_tables + static_cast<int64_t>(my_seq) * p.max_blocks_per_seq + first_page;
         auto issue_stage = [&](int64_t blk, int stage) {
           const uint32_t bar = full0 + stage * 8;
           const uint32_t dst = ring0 + stage * 2 * Gm::kPageBytes;
@@ -430,7 +435,7 @@ paged_decode_kernel(const DecodeParams p) {
         };
         const int n1 = P > warp ? (P - warp + nwarps - 1) / nwarps : 0;            // shared pages of this warp
         if (lane == 0)
-          for (int n = 0; n < S && n < n1; ++n) issue_stage(tbl_all[warp + n * nwarps], warp * S + n);
+          for (int n = 0; n < S && n < n1; ++n) issue_stage(tbl[warp + n * nwarps], warp * S + n);
 
         // B fragments of Q^T: lane holds seq n = lane / 4, elements d = 16 kk + 2 (lane % 4) + {0, 1} (+ 8)
         uint32_t qb[KD][2];
@@ -497,7 +502,7 @@ paged_decode_kernel(const DecodeParams p) {
               }
             }
             __syncwarp();
-            if (lane == 0 && n + S < n1) issue_stage(tbl_all[warp + (n + S) * nwarps], stage);
+            if (lane == 0 && n + S < n1) issue_stage(tbl[warp + (n + S) * nwarps], stage);
             if (++stage2 == S) { stage2 = 0; parity ^= 1u; }
           }
         }
@@ -552,7 +557,7 @@ paged_decode_kernel(const DecodeParams p) {
             }
             st.acc[i] = a;
           }
-          if (warp != 0) load_q(my_seq);
+          load_q(my_seq);   // not held across phase 1: its registers carry the accumulator tiles there
         }
         __syncthreads();   // partials consumed: the ring carries pages again
         // Phase 2: the pages that are this sequence's own, through the warp's own S stages
@@ -568,9 +573,23 @@ paged_decode_kernel(const DecodeParams p) {
             const int used = n1 > s2 ? (n1 - s2 + S - 1) / S : 0;                  // phases completed in phase 1
             parbits |= static_cast<uint32_t>(used & 1) << s2;
           }
-          if (lane == 0)
-            for (int n = 0; n < S && n < n_priv; ++n) issue_stage(my_tbl[P + n], warp * S + n);
+          // the sequence's own page numbers come straight from its block-table row, 32 at a time, one per lane
+          auto load_ids = [&](int batch) {
+            const int i = P + batch * kWarp + lane;
+            return i < npages_w ? __ldg(my_row + i) : 0;
+          };
+          int ids_cur = load_ids(0), ids_next = load_ids(1);
+          int batch = 0;
+          auto page_id = [&](int k) {            // k in batch or batch + 1; executed by the whole warp
+            const int a = __shfl_sync(0xffffffffu, ids_cur, k & 31), b2 = __shfl_sync(0xffffffffu, ids_next, k & 31);
+            return (k >> 5) == batch ? a : b2;
+          };
+          for (int n = 0; n < S && n < n_priv; ++n) {
+            const int blk = page_id(n);
+            if (lane == 0) issue_stage(blk, warp * S + n);
+          }
           for (int n = 0; n < n_priv; ++n) {
+            if ((n >> 5) != batch) { batch = n >> 5; ids_cur = ids_next; ids_next = load_ids(batch + 1); }
             const int s2 = n % S, stage = warp * S + s2;
             mbar_wait(full0 + stage * 8, (parbits >> s2) & 1u);
             parbits ^= 1u << s2;
@@ -580,7 +599,10 @@ paged_decode_kernel(const DecodeParams p) {
             const SmemPage vp{kp.addr + Gm::kPageBytes};
             process_page<T, D, B>(kp, vp, q, st, p.scale_log2, nvalid, pbuf0 + (n & 1) * Gm::kPbufBytes, lane);
             __syncwarp();
-            if (lane == 0 && n + S < n_priv) issue_stage(my_tbl[P + n + S], stage);
+            if (n + S < n_priv) {
+              const int blk = page_id(n + S);
+              if (lane == 0) issue_stage(blk, stage);
+            }
           }
           // this warp's result is the whole (sequence, head, split)
 #pragma unroll
@@ -788,17 +810,20 @@ struct DecodeLaunch {
 
 // bytes of dynamic shared memory a launch needs (same formula as the kernel)
 int decode_smem_bytes(int dtype, int head_size, int block_size, int pages_per_split,
-                      int warps, int stages, bool staged, int group_rows);
+                      int warps, int stages, bool staged);
 
 int launch_decode_f16(const DecodeLaunch& l);
 int launch_decode_bf16(const DecodeLaunch& l);
 int launch_decode_f32(const DecodeLaunch& l);
 
 #ifdef PA_DECODE_IMPL
-template <typename T, int D, int B, bool kStaged>
+template <typename T, int D, int B, bool kStaged, bool kGroups = false>
 static int launch_one(const DecodeLaunch& l) {
-  const SmemMap<T, D, B> map(l.params.pages_per_split, l.num_warps, l.params.num_stages, kStaged, l.params.group_rows);
-  auto kern = paged_decode_kernel<T, D, B, kStaged>;
+  if constexpr (kStaged && !kGroups && T::kSize == 2 && B % 16 == 0) {
+    if (l.params.group_rows > 1) return launch_one<T, D, B, true, true>(l);
+  }
+  const SmemMap<T, D, B> map(l.params.pages_per_split, l.num_warps, l.params.num_stages, kStaged);
+  auto kern = paged_decode_kernel<T, D, B, kStaged, kGroups>;
   if (map.total > 48 * 1024) {
     PA_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, map.total));
   }

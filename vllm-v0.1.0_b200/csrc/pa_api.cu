@@ -90,18 +90,25 @@ static int sm_count() {
 }
 
 // sibling-group detection needs one CTA warp per sequence of a group and room for the group's table slices
-static int group_rows_for(bool staged, int variant, int warps, int num_seqs, int pages_per_split, int dtype,
-                          int block_size) {
-  // the group path multiplies on the tensor cores: 16-bit types, pages of whole 16-token tiles
-  return (staged && variant != 3 && warps == kGroup && num_seqs >= 2 && pages_per_split <= 2048 &&
-          dtype != PA_F32 && block_size % 16 == 0) ? kGroup : 1;
+// Sibling groups are served together by a second instantiation of the kernel (tensor-core tiles for the
+// shared pages: 16-bit types, pages of whole 16-token tiles, one CTA warp per sequence of a group).  It
+// needs 128 registers per thread against 80, so it is used only where shared memory, not registers,
+// already bounds the resident CTAs -- elsewhere it would cost the plain path occupancy.
+constexpr int kMaxSmem = 227 * 1024;
+constexpr int kMaxSmemPerSm = 228 * 1024;
+constexpr int kGroupKernelRegs = 128;
+static int group_rows_for(bool staged, int variant, int warps, int num_seqs, int dtype, int block_size, int smem_bytes) {
+  if (!(staged && variant != 3 && warps == kGroup && num_seqs >= 2 && dtype != PA_F32 && block_size % 16 == 0)) return 1;
+  const int by_smem = kMaxSmemPerSm / (smem_bytes + 1024);
+  const int by_regs = 65536 / (kGroupKernelRegs * warps * kWarp);
+  return by_regs >= by_smem ? kGroup : 1;
 }
 
 int decode_smem_bytes(int dtype, int head_size, int block_size, int pages_per_split, int warps, int stages,
-                      bool staged, int group_rows) {
+                      bool staged) {
   const int page = head_size * block_size * dtype_size(dtype);
   const int pbuf = ((2 * block_size * dtype_size(dtype) + 15) / 16) * 16;
-  int o = ((group_rows * pages_per_split * 4 + 15) / 16) * 16;
+  int o = ((pages_per_split * 4 + 15) / 16) * 16;
   o += warps * (head_size + 2) * 4;
   o = ((o + 15) / 16) * 16;
   o += warps * pbuf;
@@ -111,7 +118,7 @@ int decode_smem_bytes(int dtype, int head_size, int block_size, int pages_per_sp
   return o;
 }
 
-constexpr int kMaxSmem = 227 * 1024;
+
 constexpr int kMaxPagesPerSplit = 8192;  // block-table slice kept in shared memory (32 KiB)
 
 // Fills the zero fields of `t`.  Returns pages_per_split through the pointer.
@@ -141,7 +148,7 @@ static int make_plan(int num_seqs, int num_heads, int head_size, int block_size,
   if (t->num_stages > 32) t->num_stages = 32;
 
   if (t->num_splits <= 0) {
-    const int smem1 = decode_smem_bytes(dtype, head_size, block_size, 64, t->num_warps, t->num_stages, staged, kGroup);
+    const int smem1 = decode_smem_bytes(dtype, head_size, block_size, 64, t->num_warps, t->num_stages, staged);
     int resident = kMaxSmem / (smem1 + 1024);
     const int by_threads = 2048 / (t->num_warps * kWarp);
     if (resident > by_threads) resident = by_threads;
@@ -166,11 +173,10 @@ static int make_plan(int num_seqs, int num_heads, int head_size, int block_size,
   *pages_per_split = pps;
 
   // shrink the ring until the CTA fits
-  const int gr = group_rows_for(staged, t->variant, t->num_warps, num_seqs, pps, dtype, block_size);
   while (staged && t->num_stages > 1 &&
-         decode_smem_bytes(dtype, head_size, block_size, pps, t->num_warps, t->num_stages, true, gr) > kMaxSmem)
+         decode_smem_bytes(dtype, head_size, block_size, pps, t->num_warps, t->num_stages, true) > kMaxSmem)
     --t->num_stages;
-  if (decode_smem_bytes(dtype, head_size, block_size, pps, t->num_warps, t->num_stages, staged, gr) > kMaxSmem)
+  if (decode_smem_bytes(dtype, head_size, block_size, pps, t->num_warps, t->num_stages, staged) > kMaxSmem)
     return set_error(PA_ERR_INVALID_ARGUMENT, "launch shape does not fit shared memory (warps %d, stages %d)",
                      t->num_warps, t->num_stages);
   return PA_OK;
@@ -228,7 +234,8 @@ static int decode(void* out, const void* query, const void* key_cache, const voi
   p.num_stages = t.num_stages;
   p.q_vec_ok = (reinterpret_cast<uintptr_t>(query) % 16 == 0) && ((q_stride * es) % 16 == 0);
   p.num_seqs = num_seqs;
-  p.group_rows = group_rows_for(t.variant >= 2, t.variant, t.num_warps, num_seqs, pps, dtype, block_size);
+  p.group_rows = group_rows_for(t.variant >= 2, t.variant, t.num_warps, num_seqs, dtype, block_size,
+                                decode_smem_bytes(dtype, head_size, block_size, pps, t.num_warps, t.num_stages, t.variant >= 2));
   if (t.num_splits > 1) {
     const size_t items = static_cast<size_t>(num_seqs) * num_heads;
     rc = get_workspace(stream, items * sizeof(uint32_t), items * t.num_splits * (head_size + 2) * sizeof(float),
