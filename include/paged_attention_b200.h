@@ -168,6 +168,47 @@ PA_API int pa_decode_attention_plan(int32_t num_seqs, int32_t num_heads,
                              pa_decode_tuning* plan_out);
 
 /* ------------------------------------------------------------------------ */
+/* prompt (prefill) attention                                               */
+/* ------------------------------------------------------------------------ */
+
+/*
+ * replaces: PagedAttention.multi_query_kv_attention
+ *           vllm/model_executor/layers/attention.py:50-70, i.e. xformers
+ *           memory_efficient_attention_forward with
+ *           BlockDiagonalCausalMask.from_seqlens(prompt_lens)
+ *           (vllm/model_executor/input_metadata.py:33); parity reference
+ *           tests/kernels/test_attention.py:69-101 (ref_multi_query_kv_attention)
+ *
+ * Causal self-attention over num_seqs prompts packed along the token dimension
+ * (prompt i occupies tokens [sum(seq_lens[:i]), sum(seq_lens[:i+1]))):
+ *   out[t][h][:] = softmax_{u <= t, same prompt}(scale * q[t][h] . k[u][h]) . v[u][h]
+ * query / key / value / out are [num_tokens][num_heads][head_size] views with
+ * token strides *_stride (elements; 3*num_heads*head_size when sliced from the
+ * fused qkv tensor), inner dimensions contiguous, rows 16-byte aligned.
+ * seq_lens is a HOST array (the reference holds prompt_lens as a Python list).
+ * head_size in {64, 80, 96, 128}.  PA_F16 / PA_BF16 run on the tcgen05 tensor
+ * cores (TMA-fed, accumulators in tensor memory); PA_F32 takes an exact fp32
+ * SIMT path.  Tokens past sum(seq_lens) (the padding the model adds) are not
+ * read or written.
+ */
+PA_API int pa_prefill_attention(void* out, const void* query, const void* key,
+                         const void* value, const int32_t* seq_lens,
+                         int32_t num_seqs, int32_t num_heads, int32_t head_size,
+                         int64_t q_stride, int64_t k_stride, int64_t v_stride,
+                         int64_t out_stride, float scale, int32_t dtype,
+                         void* stream);
+
+/* Same, and (16-bit types) CTA (head 0, first tile) also dumps to `debug` (device, floats):
+ * [128][128] raw q.k of its first K/V tile, [128][64 or 128] unnormalised output rows,
+ * [128] row sums, [128] row maxima (log2 domain).  Tests only. */
+PA_API int pa_prefill_attention_debug(void* out, const void* query, const void* key,
+                               const void* value, const int32_t* seq_lens,
+                               int32_t num_seqs, int32_t num_heads, int32_t head_size,
+                               int64_t q_stride, int64_t k_stride, int64_t v_stride,
+                               int64_t out_stride, float scale, int32_t dtype,
+                               float* debug, void* stream);
+
+/* ------------------------------------------------------------------------ */
 /* KV-cache movers (bit-exact)                                              */
 /* ------------------------------------------------------------------------ */
 

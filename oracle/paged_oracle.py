@@ -8,6 +8,7 @@ instead):
 
   decode_attention_loop   tests/kernels/test_attention.py:30-66  (ref_single_query_cached_kv_attention)
                           + :14-27 (ref_masked_attention)
+  prefill_attention_loop  tests/kernels/test_attention.py:69-101 (ref_multi_query_kv_attention)
   reshape_and_cache       tests/kernels/test_cache.py:95-100
   gather_cached_kv        tests/kernels/test_cache.py:138-143
   copy_blocks             tests/kernels/test_cache.py:51-56
@@ -106,6 +107,47 @@ def decode_attention_fp32(query: torch.Tensor, key_cache: torch.Tensor, value_ca
         probs = torch.softmax(scores, dim=-1)
         out[i] = torch.einsum("hk,khd->hd", probs, v)
     return out
+
+
+# ---------------------------------------------------------------------------
+# prompt (prefill) attention
+# ---------------------------------------------------------------------------
+@torch.inference_mode()
+def prefill_attention_loop(seq_lens: Sequence[int], query: torch.Tensor, key: torch.Tensor, value: torch.Tensor,
+                           scale: Optional[float] = None) -> torch.Tensor:
+    """Per-prompt dense causal attention (test_attention.py:69-101): an additive upper-triangular
+    mask of finfo(dtype).min, scores / softmax in the input dtype (:14-27).  query/key/value are
+    [num_tokens, num_heads, head_size]; prompts are packed along the token dimension."""
+    dtype = query.dtype
+    if scale is None:
+        scale = 1.0 / (query.shape[-1] ** 0.5)
+    outs, start = [], 0
+    for n in seq_lens:
+        end = start + int(n)
+        mask = torch.triu(torch.ones(n, n, dtype=dtype), diagonal=1) * torch.finfo(dtype).min
+        scores = torch.einsum("qhd,khd->hqk", query[start:end] * scale, key[start:end]) + mask
+        probs = torch.softmax(scores, dim=-1)
+        outs.append(torch.einsum("hqk,khd->qhd", probs, value[start:end]))
+        start = end
+    return torch.cat(outs, dim=0) if outs else query[:0].clone()
+
+
+@torch.inference_mode()
+def prefill_attention_fp32(seq_lens: Sequence[int], query: torch.Tensor, key: torch.Tensor, value: torch.Tensor,
+                           scale: Optional[float] = None) -> torch.Tensor:
+    """Same attention with every intermediate in fp32 on the (already rounded) inputs: the yardstick
+    for unit-scale inputs, where the reference's in-dtype softmax is itself only ~1e-3 accurate."""
+    if scale is None:
+        scale = 1.0 / (query.shape[-1] ** 0.5)
+    q, k, v = query.float(), key.float(), value.float()
+    outs, start = [], 0
+    for n in seq_lens:
+        end = start + int(n)
+        scores = torch.einsum("qhd,khd->hqk", q[start:end], k[start:end]) * scale
+        scores = scores.masked_fill(torch.triu(torch.ones(n, n, dtype=torch.bool), diagonal=1), float("-inf"))
+        outs.append(torch.einsum("hqk,khd->qhd", torch.softmax(scores, dim=-1), v[start:end]))
+        start = end
+    return torch.cat(outs, dim=0) if outs else q[:0].clone()
 
 
 # ---------------------------------------------------------------------------

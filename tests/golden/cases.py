@@ -119,6 +119,28 @@ def rope_case(case_id: str) -> Dict[str, object]:
             "max_position": max_position, "qkv": qkv, "positions": positions}
 
 
+def prefill_case_ids() -> List[str]:
+    ids = [f"{dt}-d{d}-ref" for dt in DTYPES for d in HEAD_SIZES]
+    ids += [f"{dt}-d{d}-unit" for dt in DTYPES for d in (128, 80)]
+    return ids
+
+
+def prefill_case(case_id: str) -> Dict[str, object]:
+    """Prompt attention: 4 prompts packed along the token dimension (lengths 1, 130, 70 and 128: a
+    single token, one that crosses a 128-row tile, a short one, and exactly one tile), 3 heads,
+    q/k/v sliced out of a fused qkv tensor as the model does (test_attention.py:236-239)."""
+    dt, d, dist = case_id.split("-")
+    dtype, head_size = DTYPES[dt], int(d[1:])
+    seed = int(hashlib.sha256(("prefill-" + case_id).encode()).hexdigest()[:8], 16)
+    rs = np.random.RandomState(seed)
+    seq_lens = [1, 130, 70, 128]
+    num_heads = 3
+    qkv = _tensor(rs, (sum(seq_lens), 3, num_heads, head_size), dtype, dist)
+    return {"dtype": dtype, "head_size": head_size, "num_heads": num_heads, "seq_lens": seq_lens,
+            "scale": float(1.0 / (head_size ** 0.5)), "qkv": qkv,
+            "query": qkv[:, 0], "key": qkv[:, 1], "value": qkv[:, 2]}
+
+
 def to_numpy(t: torch.Tensor) -> np.ndarray:
     """Bit pattern of a tensor as a numpy array (bf16/f16 -> uint16)."""
     t = t.contiguous()

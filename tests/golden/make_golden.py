@@ -10,6 +10,8 @@ source with `ast` and executed unmodified:
 
   tests/kernels/test_attention.py  ref_masked_attention (:14-27),
                                    ref_single_query_cached_kv_attention (:30-66)
+                                   ref_multi_query_kv_attention (:69-101), with device='cuda' of its
+                                   mask (:87) mapped to the CPU while it runs
   tests/kernels/test_cache.py      the reference loops inside run_copy_blocks (:51-56),
                                    run_reshape_and_cache (:95-100), run_gather_cached_kv (:138-143)
   tests/kernels/test_pos_encoding.py  rotate_half, apply_rotary_pos_emb, RefRotaryEmbeddingNeox (:12-77)
@@ -157,12 +159,45 @@ def make_rope() -> None:
     json.dump(meta, open(os.path.join(HERE, "rope_inputs.sha256.json"), "w"), indent=1, sort_keys=True)
 
 
+def make_prefill() -> None:
+    ns = _functions(os.path.join(REF, "tests/kernels/test_attention.py"),
+                    {"ref_masked_attention", "ref_multi_query_kv_attention"})
+    ref = ns["ref_multi_query_kv_attention"]
+    # the reference moves its mask to 'cuda' (:87); there is no GPU here, so .to() is told to stay on the CPU
+    real_to = torch.Tensor.to
+
+    def cpu_to(self, *args, **kwargs):
+        if kwargs.get("device") == "cuda":
+            kwargs["device"] = "cpu"
+        return real_to(self, *args, **kwargs)
+
+    out, meta = {}, {}
+    torch.Tensor.to = cpu_to
+    try:
+        for cid in cases.prefill_case_ids():
+            c = cases.prefill_case(cid)
+            cu = [0]
+            for n in c["seq_lens"]:
+                cu.append(cu[-1] + n)
+            with torch.inference_mode():
+                o = ref(cu, c["query"], c["key"], c["value"], c["dtype"])
+            out[cid] = cases.to_numpy(o)
+            meta[cid] = cases.digest(c["qkv"])
+            print(cid, float(o.float().abs().max()))
+    finally:
+        torch.Tensor.to = real_to
+    np.savez_compressed(os.path.join(HERE, "prefill_golden.npz"), **out)
+    json.dump(meta, open(os.path.join(HERE, "prefill_inputs.sha256.json"), "w"), indent=1, sort_keys=True)
+
+
 if __name__ == "__main__":
     torch.manual_seed(0)
-    which = sys.argv[1:] or ["attention", "cache", "rope"]
+    which = sys.argv[1:] or ["attention", "cache", "rope", "prefill"]
     if "attention" in which:
         make_attention()
     if "cache" in which:
         make_cache()
     if "rope" in which:
         make_rope()
+    if "prefill" in which:
+        make_prefill()

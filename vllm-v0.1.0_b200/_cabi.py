@@ -44,6 +44,10 @@ SIGNATURES = {
     "pa_decode_attention_ex": (C.c_int, [_vp, _vp, _vp, _vp, _f32, _vp, _vp, _i32, _i32, _i32, _i32, _i32, _i32,
                                          _i64, _i32, C.POINTER(DecodeTuning), _vp]),
     "pa_decode_attention_plan": (C.c_int, [_i32, _i32, _i32, _i32, _i32, _i32, C.POINTER(DecodeTuning)]),
+    "pa_prefill_attention": (C.c_int, [_vp, _vp, _vp, _vp, C.POINTER(_i32), _i32, _i32, _i32, _i64, _i64, _i64, _i64,
+                                       _f32, _i32, _vp]),
+    "pa_prefill_attention_debug": (C.c_int, [_vp, _vp, _vp, _vp, C.POINTER(_i32), _i32, _i32, _i32, _i64, _i64, _i64,
+                                             _i64, _f32, _i32, _vp, _vp]),
     "pa_reshape_and_cache": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _i64, _i64, _i32, _vp]),
     "pa_gather_cached_kv": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _i64, _i64, _i32, _vp]),
     "pa_rotary_embedding_neox": (C.c_int, [_vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _i64, _i64, _i32, _vp]),

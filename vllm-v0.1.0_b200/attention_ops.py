@@ -103,3 +103,52 @@ def decode_plan(num_seqs: int, num_heads: int, head_size: int, block_size: int, 
     _cabi.check(_cabi.lib().pa_decode_attention_plan(num_seqs, num_heads, head_size, block_size, max_context_len,
                                                      _DTYPES[dtype], C.byref(plan)))
     return plan
+
+
+def multi_query_kv_attention(
+    output: torch.Tensor,         # [num_prompt_tokens, num_heads, head_size]
+    query: torch.Tensor,          # [num_prompt_tokens, num_heads, head_size], row-strided
+    key: torch.Tensor,            # same
+    value: torch.Tensor,          # same
+    prompt_lens,                  # List[int]: the prompts packed along the token dimension
+    scale: float,
+    *,
+    debug: Optional[torch.Tensor] = None,
+) -> None:
+    """Causal self-attention of every prompt over its own tokens, written into `output`.
+
+    Replaces PagedAttention.multi_query_kv_attention (vllm/model_executor/layers/attention.py:50-70:
+    xformers memory_efficient_attention_forward under BlockDiagonalCausalMask.from_seqlens(prompt_lens));
+    the mask is passed as the list of prompt lengths it was built from.  fp16 / bf16 run on the
+    tcgen05 tensor cores, fp32 on an exact SIMT path.  `debug` (tests): float32 device buffer the
+    first CTA dumps its raw tiles into.
+    """
+    dev = query.device
+    for name, t in (("output", output), ("query", query), ("key", key), ("value", value)):
+        _require_cuda(name, t, dev)
+    code = _dtype_code(query)
+    if not (output.dtype == query.dtype == key.dtype == value.dtype):
+        raise RuntimeError("output, query, key and value must share one dtype")
+    if query.dim() != 3 or key.shape != query.shape or value.shape != query.shape or output.shape != query.shape:
+        raise RuntimeError("output, query, key and value must be [num_tokens, num_heads, head_size] of one shape")
+    num_tokens, num_heads, head_size = query.shape
+    for name, t in (("output", output), ("query", query), ("key", key), ("value", value)):
+        if t.stride(2) != 1 or t.stride(1) != head_size:
+            raise RuntimeError(f"{name} must be contiguous in its last two dimensions")
+    lens = [int(n) for n in prompt_lens]
+    if sum(lens) > num_tokens:
+        raise RuntimeError("prompt_lens add up to more tokens than query holds")
+    arr = (C.c_int32 * max(1, len(lens)))(*lens)
+    lib = _cabi.lib()
+    stream = torch.cuda.current_stream(dev).cuda_stream
+    with torch.cuda.device(dev):
+        if debug is None:
+            rc = lib.pa_prefill_attention(output.data_ptr(), query.data_ptr(), key.data_ptr(), value.data_ptr(), arr,
+                                          len(lens), num_heads, head_size, query.stride(0), key.stride(0),
+                                          value.stride(0), output.stride(0), float(scale), code, stream)
+        else:
+            rc = lib.pa_prefill_attention_debug(output.data_ptr(), query.data_ptr(), key.data_ptr(), value.data_ptr(),
+                                                arr, len(lens), num_heads, head_size, query.stride(0), key.stride(0),
+                                                value.stride(0), output.stride(0), float(scale), code,
+                                                debug.data_ptr(), stream)
+    _cabi.check(rc)
