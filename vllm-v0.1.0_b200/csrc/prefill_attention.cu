@@ -29,240 +29,9 @@
 
 #include <math_constants.h>
 
-#include "tc05.cuh"
+#include "prefill_tc.cuh"
 
 namespace pa {
-
-constexpr int kPfRows = 128;       // query rows per CTA = TMEM lanes
-constexpr int kPfCols = 128;       // K/V tokens per tile
-constexpr int kPfMaxTiles = 1024;  // tiles per launch (the table travels as a kernel parameter)
-
-struct PrefillTiles {
-  int32_t tok0[kPfMaxTiles];  // first token of the prompt in the packed batch
-  int32_t len[kPfMaxTiles];   // prompt length
-  int32_t q0[kPfMaxTiles];    // first query row of this tile inside the prompt (multiple of 128)
-};
-
-struct PrefillParams {
-  void* out;
-  int64_t out_stride;  // elements between consecutive tokens of out
-  int32_t num_heads;
-  int32_t head_size;
-  float scale_log2;
-  float* dbg;          // tests: raw S of the first tile, raw O, row sums of CTA (0, 0)
-};
-
-__device__ __forceinline__ float ex2(float x) {   // exp2(-inf) == 0
-  float y;
-  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
-  return y;
-}
-
-// tensor-memory columns
-constexpr uint32_t kTmS0 = 0, kTmS1 = 128, kTmO = 256, kTmP = 384, kTmCols = 512;
-
-template <typename T, int DP>
-__global__ void __launch_bounds__(128, 1)
-prefill_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant__ CUtensorMap tmk,
-                  const __grid_constant__ CUtensorMap tmv, const __grid_constant__ PrefillTiles tiles,
-                  const PrefillParams p) {
-  constexpr int kAtoms = DP / 64;                 // 64-element (128-byte) column groups of a tile
-  constexpr uint32_t kAtomBytes = 128 * 128;      // 128 rows x 128 bytes
-  constexpr uint32_t kTileBytes = kAtoms * kAtomBytes;
-  constexpr bool kBf16 = T::kId == PA_BF16;
-  constexpr uint32_t kIdescQK = tc05::instr_desc_f16(kBf16, 128, 128, false, false);
-  constexpr uint32_t kIdescPV = tc05::instr_desc_f16(kBf16, 128, DP, false, true);
-
-  extern __shared__ unsigned char smem_raw[];
-  const uint32_t base = (smem_addr(smem_raw) + 1023u) & ~1023u;
-  const uint32_t sQ = base;
-  const uint32_t sK = sQ + kTileBytes;            // two stages
-  const uint32_t sV = sK + 2 * kTileBytes;        // two stages
-  const uint32_t sBar = sV + 2 * kTileBytes;
-  const uint32_t bar_q = sBar, bar_k = sBar + 8, bar_v = sBar + 24, bar_s = sBar + 40, bar_o = sBar + 56;
-  const uint32_t tm_slot = sBar + 64;
-
-  const int tid = threadIdx.x, warp = tid >> 5;
-  const int head = blockIdx.x;
-  const int tok0 = tiles.tok0[blockIdx.y], len = tiles.len[blockIdx.y], q0 = tiles.q0[blockIdx.y];
-  const int kv_end = min(q0 + kPfRows, len);      // causal: nothing right of the diagonal tile
-  const int ntiles = (kv_end + kPfCols - 1) / kPfCols;
-
-  if (tid == 0) {
-    tc05::tma_prefetch_desc(&tmq); tc05::tma_prefetch_desc(&tmk); tc05::tma_prefetch_desc(&tmv);
-    mbar_init(bar_q, 1);
-    for (int s = 0; s < 2; ++s) { mbar_init(bar_k + 8 * s, 1); mbar_init(bar_v + 8 * s, 1); mbar_init(bar_s + 8 * s, 1); }
-    mbar_init(bar_o, 1);
-    mbar_init_fence();
-  }
-  if (warp == 0) { __syncwarp(); tc05::tmem_alloc<kTmCols>(tm_slot); }
-  tc05::fence_before_sync();
-  __syncthreads();
-  tc05::fence_after_sync();
-  uint32_t tmem;
-  asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem) : "r"(tm_slot) : "memory");
-  const uint32_t lane_base = tmem + (static_cast<uint32_t>(warp * 32) << 16);   // this warp's 32 TMEM lanes
-
-  auto load_tile = [&](const CUtensorMap* map, uint32_t dst, int row0, uint32_t bar) {
-    mbar_expect_tx(bar, kTileBytes);
-#pragma unroll
-    for (int a = 0; a < kAtoms; ++a) tc05::tma_load_3d(dst + a * kAtomBytes, map, a * 64, head, row0, bar);
-  };
-  auto issue_qk = [&](int j) {                     // S[j & 1] = Q . K_j^T
-    const uint32_t kb = sK + (j & 1) * kTileBytes;
-#pragma unroll
-    for (int kk = 0; kk < DP / 16; ++kk) {
-      const uint32_t off = (kk >> 2) * kAtomBytes + (kk & 3) * 32;
-      tc05::mma_ss(tmem + ((j & 1) ? kTmS1 : kTmS0), tc05::smem_desc_sw128(sQ + off, 16, 1024),
-                   tc05::smem_desc_sw128(kb + off, 16, 1024), kIdescQK, kk > 0);
-    }
-    tc05::mma_commit(bar_s + 8 * (j & 1));
-  };
-  auto issue_pv = [&](int j) {                     // O (+)= P . V_j
-    const uint32_t vb = sV + (j & 1) * kTileBytes;
-#pragma unroll
-    for (int kk = 0; kk < kPfCols / 16; ++kk)
-      tc05::mma_ts(tmem + kTmO, tmem + kTmP + kk * 8, tc05::smem_desc_sw128(vb + kk * 2048, kAtomBytes, 1024),
-                   kIdescPV, j > 0 || kk > 0);
-    tc05::mma_commit(bar_o);
-  };
-
-  if (tid == 0) {
-    load_tile(&tmq, sQ, tok0 + q0, bar_q);
-    for (int j = 0; j < 2 && j < ntiles; ++j) {
-      load_tile(&tmk, sK + j * kTileBytes, tok0 + j * kPfCols, bar_k + 8 * j);
-      load_tile(&tmv, sV + j * kTileBytes, tok0 + j * kPfCols, bar_v + 8 * j);
-    }
-    mbar_wait(bar_q, 0);
-    mbar_wait(bar_k, 0);
-    tc05::fence_after_sync();
-    issue_qk(0);
-  }
-  __syncwarp();
-
-  float m_run = -CUDART_INF_F, l_run = 0.f;
-  const int r = tid;                                // row of this thread inside the tile
-  for (int j = 0; j < ntiles; ++j) {
-    if (tid == 0 && j + 1 < ntiles) {               // keep the tensor core busy during this tile's softmax
-      mbar_wait(bar_k + 8 * ((j + 1) & 1), ((j + 1) >> 1) & 1);
-      tc05::fence_after_sync();
-      issue_qk(j + 1);
-    }
-    __syncwarp();
-    mbar_wait(bar_s + 8 * (j & 1), (j >> 1) & 1);
-    tc05::fence_after_sync();
-    if (tid == 0 && j + 2 < ntiles)                 // K stage j & 1 is free again
-      load_tile(&tmk, sK + (j & 1) * kTileBytes, tok0 + (j + 2) * kPfCols, bar_k + 8 * (j & 1));
-    __syncwarp();
-
-    // ---- logits of this row -------------------------------------------------------------
-    uint32_t s[4][32];
-#pragma unroll
-    for (int c = 0; c < 4; ++c) tc05::tmem_ld32(lane_base + ((j & 1) ? kTmS1 : kTmS0) + c * 32, s[c]);
-    tc05::tmem_wait_ld();
-    if (p.dbg && blockIdx.x == 0 && blockIdx.y == 0 && j == 0) {
-#pragma unroll
-      for (int c = 0; c < 4; ++c)
-#pragma unroll
-        for (int i = 0; i < 32; ++i) p.dbg[r * 128 + c * 32 + i] = __uint_as_float(s[c][i]);
-    }
-    const bool diag = j == ntiles - 1;              // the only tile that needs masking
-    const int lim = min(r, len - 1 - q0);           // last valid column of this row in the diagonal tile
-    float mx = -CUDART_INF_F;
-#pragma unroll
-    for (int c = 0; c < 4; ++c)
-#pragma unroll
-      for (int i = 0; i < 32; ++i) {
-        float v = __uint_as_float(s[c][i]) * p.scale_log2;
-        if (diag && c * 32 + i > lim) v = -CUDART_INF_F;
-        s[c][i] = __float_as_uint(v);
-        mx = fmaxf(mx, v);
-      }
-    const float m_new = fmaxf(m_run, mx);
-    const float m_use = m_new == -CUDART_INF_F ? 0.f : m_new;   // row with nothing valid yet (beyond len)
-    const float alpha = ex2(m_run - m_use);
-    float sum = 0.f;
-    uint32_t pk[2][32];
-#pragma unroll
-    for (int c = 0; c < 4; ++c)
-#pragma unroll
-      for (int i = 0; i < 32; i += 2) {
-        const float p0 = ex2(__uint_as_float(s[c][i]) - m_use);
-        const float p1 = ex2(__uint_as_float(s[c][i + 1]) - m_use);
-        sum += p0 + p1;
-        pk[c >> 1][(c & 1) * 16 + (i >> 1)] = pack2<T>(p0, p1);
-      }
-    l_run = l_run * alpha + sum;
-    m_run = m_new;
-
-    // ---- previous P.V must be done before P and O are touched ------------------------------
-    if (j > 0) {
-      mbar_wait(bar_o, (j - 1) & 1);
-      tc05::fence_after_sync();
-      if (tid == 0 && j + 1 < ntiles)               // V stage (j + 1) & 1 is free again
-        load_tile(&tmv, sV + ((j + 1) & 1) * kTileBytes, tok0 + (j + 1) * kPfCols, bar_v + 8 * ((j + 1) & 1));
-      __syncwarp();
-      if (__any_sync(0xffffffffu, alpha != 1.f)) {
-#pragma unroll
-        for (int c = 0; c < DP / 32; ++c) {
-          uint32_t o[32];
-          tc05::tmem_ld32(lane_base + kTmO + c * 32, o);
-          tc05::tmem_wait_ld();
-#pragma unroll
-          for (int i = 0; i < 32; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
-          tc05::tmem_st32(lane_base + kTmO + c * 32, o);
-        }
-      }
-    }
-    tc05::tmem_st32(lane_base + kTmP, pk[0]);
-    tc05::tmem_st32(lane_base + kTmP + 32, pk[1]);
-    tc05::tmem_wait_st();
-    tc05::fence_before_sync();
-    __syncthreads();
-    if (tid == 0) {
-      tc05::fence_after_sync();
-      mbar_wait(bar_v + 8 * (j & 1), (j >> 1) & 1);
-      issue_pv(j);
-    }
-    __syncwarp();
-  }
-
-  // ---- epilogue: O / l -> out ---------------------------------------------------------------
-  mbar_wait(bar_o, (ntiles - 1) & 1);
-  tc05::fence_after_sync();
-  const int D = p.head_size;
-  const bool row_ok = q0 + r < len;
-  const float inv = 1.f / l_run;
-  char* orow = reinterpret_cast<char*>(p.out) +
-               ((static_cast<int64_t>(tok0) + q0 + r) * p.out_stride + static_cast<int64_t>(head) * D) * 2;
-#pragma unroll
-  for (int c = 0; c < DP / 32; ++c) {
-    uint32_t o[32];
-    tc05::tmem_ld32(lane_base + kTmO + c * 32, o);
-    tc05::tmem_wait_ld();
-    if (p.dbg && blockIdx.x == 0 && blockIdx.y == 0) {
-#pragma unroll
-      for (int i = 0; i < 32; ++i) p.dbg[128 * 128 + r * DP + c * 32 + i] = __uint_as_float(o[i]);
-      if (c == 0) { p.dbg[128 * 128 + 128 * DP + r] = l_run; p.dbg[128 * 128 + 128 * DP + 128 + r] = m_run; }
-    }
-    if (row_ok) {
-#pragma unroll
-      for (int v = 0; v < 4; ++v) {                 // 8 elements = 16 bytes per store
-        if (c * 32 + v * 8 < D) {
-          uint4 w;
-          w.x = pack2<T>(__uint_as_float(o[v * 8 + 0]) * inv, __uint_as_float(o[v * 8 + 1]) * inv);
-          w.y = pack2<T>(__uint_as_float(o[v * 8 + 2]) * inv, __uint_as_float(o[v * 8 + 3]) * inv);
-          w.z = pack2<T>(__uint_as_float(o[v * 8 + 4]) * inv, __uint_as_float(o[v * 8 + 5]) * inv);
-          w.w = pack2<T>(__uint_as_float(o[v * 8 + 6]) * inv, __uint_as_float(o[v * 8 + 7]) * inv);
-          *reinterpret_cast<uint4*>(orow + (c * 32 + v * 8) * 2) = w;
-        }
-      }
-    }
-  }
-  tc05::fence_before_sync();
-  __syncthreads();
-  if (warp == 0) tc05::tmem_free<kTmCols>(tmem);
-}
 
 // ---------------------------------------------------------------------------
 // fp32: exact SIMT path.  CTA = 64 query rows x 2 threads (each owns half of the head dimension);
@@ -365,10 +134,10 @@ static int make_qkv_map(CUtensorMap* map, const void* base, int dtype, int head_
 template <typename T, int DP>
 static int launch_tc(const CUtensorMap& mq, const CUtensorMap& mk, const CUtensorMap& mv, const PrefillTiles& tiles,
                      int ntiles, const PrefillParams& p, cudaStream_t stream) {
-  constexpr int smem = 5 * (DP / 64) * 128 * 128 + 1024 + 128;
+  constexpr int smem = 6 * (DP / 64) * 128 * 128 + 1024 + 128;
   auto kern = prefill_tc_kernel<T, DP>;
   PA_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-  kern<<<dim3(p.num_heads, ntiles), 128, smem, stream>>>(mq, mk, mv, tiles, p);
+  kern<<<dim3(p.num_heads, ntiles), kPfThreads, smem, stream>>>(mq, mk, mv, tiles, p);
   count_launch();
   return check_cuda(cudaGetLastError(), "prefill_tc_kernel launch");
 }

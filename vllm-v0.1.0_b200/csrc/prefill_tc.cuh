@@ -1,0 +1,284 @@
+// tcgen05 prompt-attention kernel (16-bit types).  See prefill_attention.cu for the operator.
+//
+// One CTA = 256 query rows of one (prompt, head), as two 128-row tiles A and B that share every K/V
+// tile.  Twelve warps (two of them only donate their registers), three roles:
+//   warps 0-3 / 4-7  softmax group of tile A / B: thread r owns row r (TMEM lane r % 128)
+//   warp 8           TMA producer: Q tiles once, then K_j / V_j through two-stage rings
+//   warp 9           MMA issuer: one thread issues every tcgen05.mma of the CTA
+// Tensor memory (512 columns): S_A | S_B | O_A | O_B, 128 fp32 columns each; the probabilities
+// P_i overwrite the first 64 columns of S_i (two 16-bit values per column) and are consumed
+// from there as the A operand of P.V.  Per tile the dependency chain is
+//   Q.K_j^T -> S_i --softmax group i--> P_i -> O_i += P_i.V_j, then Q.K_{j+1}^T into S_i again;
+// the issuer interleaves the chains of A and B, so the tensor core works on one tile's matrices
+// while the other tile's threads are in their softmax.  tcgen05.mma executes in issue order, which
+// is what makes the S_i / P_i aliasing safe without an extra barrier.
+#pragma once
+
+#include <math_constants.h>
+
+#include "tc05.cuh"
+
+namespace pa {
+
+constexpr int kPfRows = 256;       // query rows per CTA (two tiles of 128 = TMEM lanes)
+constexpr int kPfCols = 128;       // K/V tokens per tile
+constexpr int kPfMaxTiles = 1024;  // CTAs per launch (the table travels as a kernel parameter)
+constexpr int kPfThreads = 384;   // 8 softmax warps + producer + issuer + 2 idle warps that only donate registers
+
+struct PrefillTiles {
+  int32_t tok0[kPfMaxTiles];  // first token of the prompt in the packed batch
+  int32_t len[kPfMaxTiles];   // prompt length
+  int32_t q0[kPfMaxTiles];    // first query row of this CTA inside the prompt (multiple of its row count)
+};
+
+struct PrefillParams {
+  void* out;
+  int64_t out_stride;  // elements between consecutive tokens of out
+  int32_t num_heads;
+  int32_t head_size;
+  float scale_log2;
+  float* dbg;          // tests: raw S of the first tile, raw O, row sums / maxima of tile A of CTA (0, 0)
+};
+
+__device__ __forceinline__ float ex2(float x) {   // exp2(-inf) == 0
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
+template <typename T, int DP>
+__global__ void __launch_bounds__(kPfThreads, 1)
+prefill_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant__ CUtensorMap tmk,
+                  const __grid_constant__ CUtensorMap tmv, const __grid_constant__ PrefillTiles tiles,
+                  const PrefillParams p) {
+  constexpr int kAtoms = DP / 64;                 // 64-element (128-byte) column groups of a tile
+  constexpr uint32_t kAtomBytes = 128 * 128;      // 128 rows x 128 bytes
+  constexpr uint32_t kTileBytes = kAtoms * kAtomBytes;
+  constexpr bool kBf16 = T::kId == PA_BF16;
+  constexpr uint32_t kIdescQK = tc05::instr_desc_f16(kBf16, 128, 128, false, false);
+  constexpr uint32_t kIdescPV = tc05::instr_desc_f16(kBf16, 128, DP, false, true);
+  constexpr uint32_t kTmS = 0, kTmO = 256, kTmCols = 512;   // S_i at 128 i, O_i at 256 + 128 i
+
+  extern __shared__ unsigned char smem_raw[];
+  const uint32_t base = (smem_addr(smem_raw) + 1023u) & ~1023u;
+  const uint32_t sQ = base;                        // two tiles
+  const uint32_t sK = sQ + 2 * kTileBytes;         // two stages
+  const uint32_t sV = sK + 2 * kTileBytes;         // two stages
+  const uint32_t sBar = sV + 2 * kTileBytes;
+  const uint32_t bar_q = sBar;                     // Q tiles landed
+  const uint32_t bar_kf = sBar + 8, bar_ke = sBar + 24, bar_vf = sBar + 40, bar_ve = sBar + 56;   // [2] each
+  const uint32_t bar_s = sBar + 72, bar_p = sBar + 88, bar_o = sBar + 104;                        // [2] each
+  const uint32_t tm_slot = sBar + 120;
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int head = blockIdx.x;
+  const int tok0 = tiles.tok0[blockIdx.y], len = tiles.len[blockIdx.y], q0 = tiles.q0[blockIdx.y];
+  // K/V tiles each query tile visits: everything up to and including its diagonal tile
+  const int nA = q0 / kPfCols + 1;
+  const int nB = (q0 + 128 < len) ? nA + 1 : 0;
+  const int nmax = nB > nA ? nB : nA;
+
+  if (tid == 0) {
+    tc05::tma_prefetch_desc(&tmq); tc05::tma_prefetch_desc(&tmk); tc05::tma_prefetch_desc(&tmv);
+    mbar_init(bar_q, 1);
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(bar_kf + 8 * s, 1); mbar_init(bar_ke + 8 * s, 1);
+      mbar_init(bar_vf + 8 * s, 1); mbar_init(bar_ve + 8 * s, 1);
+      mbar_init(bar_s + 8 * s, 1); mbar_init(bar_p + 8 * s, 128); mbar_init(bar_o + 8 * s, 1);
+    }
+    mbar_init_fence();
+  }
+  if (warp == 0) { __syncwarp(); tc05::tmem_alloc<kTmCols>(tm_slot); }
+  tc05::fence_before_sync();
+  __syncthreads();
+  tc05::fence_after_sync();
+  uint32_t tmem;
+  asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem) : "r"(tm_slot) : "memory");
+
+  if (warp == 8) {
+    // ===================== TMA producer =====================
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
+    if (lane == 0) {
+      auto load_tile = [&](const CUtensorMap* map, uint32_t dst, int row0, uint32_t bar) {
+#pragma unroll
+        for (int a = 0; a < kAtoms; ++a) tc05::tma_load_3d(dst + a * kAtomBytes, map, a * 64, head, row0, bar);
+      };
+      mbar_expect_tx(bar_q, (nB ? 2 : 1) * kTileBytes);
+      load_tile(&tmq, sQ, tok0 + q0, bar_q);
+      if (nB) load_tile(&tmq, sQ + kTileBytes, tok0 + q0 + 128, bar_q);
+      for (int j = 0; j < nmax; ++j) {
+        const int s = j & 1;
+        const uint32_t ph = ((j >> 1) & 1) ^ 1;    // first use of a stage passes immediately
+        mbar_wait(bar_ke + 8 * s, ph);
+        mbar_expect_tx(bar_kf + 8 * s, kTileBytes);
+        load_tile(&tmk, sK + s * kTileBytes, tok0 + j * kPfCols, bar_kf + 8 * s);
+        mbar_wait(bar_ve + 8 * s, ph);
+        mbar_expect_tx(bar_vf + 8 * s, kTileBytes);
+        load_tile(&tmv, sV + s * kTileBytes, tok0 + j * kPfCols, bar_vf + 8 * s);
+      }
+    }
+  } else if (warp == 9) {
+    // ===================== MMA issuer =====================
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
+    if (lane == 0) {
+      auto issue_qk = [&](int i, int j) {           // S_i = Q_i . K_j^T
+        const uint32_t qb = sQ + i * kTileBytes, kb = sK + (j & 1) * kTileBytes;
+#pragma unroll
+        for (int kk = 0; kk < DP / 16; ++kk) {
+          const uint32_t off = (kk >> 2) * kAtomBytes + (kk & 3) * 32;
+          tc05::mma_ss(tmem + kTmS + 128 * i, tc05::smem_desc_sw128(qb + off, 16, 1024),
+                       tc05::smem_desc_sw128(kb + off, 16, 1024), kIdescQK, kk > 0);
+        }
+      };
+      auto issue_pv = [&](int i, int j) {           // O_i (+)= P_i . V_j
+        const uint32_t vb = sV + (j & 1) * kTileBytes;
+#pragma unroll
+        for (int kk = 0; kk < kPfCols / 16; ++kk)
+          tc05::mma_ts(tmem + kTmO + 128 * i, tmem + kTmS + 128 * i + kk * 8,
+                       tc05::smem_desc_sw128(vb + kk * 2048, kAtomBytes, 1024), kIdescPV, j > 0 || kk > 0);
+      };
+      mbar_wait(bar_q, 0);
+      mbar_wait(bar_kf, 0);
+      tc05::fence_after_sync();
+      issue_qk(0, 0);
+      tc05::mma_commit(bar_s);
+      if (nB) { issue_qk(1, 0); tc05::mma_commit(bar_s + 8); }
+      tc05::mma_commit(bar_ke);                     // K_0 is free once these have run
+      for (int j = 0; j < nmax; ++j) {
+        const int s = j & 1;
+        const bool more_k = j + 1 < nmax;
+        if (more_k) { mbar_wait(bar_kf + 8 * (s ^ 1), ((j + 1) >> 1) & 1); }
+        mbar_wait(bar_vf + 8 * s, (j >> 1) & 1);
+#pragma unroll
+        for (int i = 0; i < 2; ++i) {
+          const int ni = i ? nB : nA;
+          if (j < ni) {
+            mbar_wait(bar_p + 8 * i, j & 1);         // P_i of tile j is in tensor memory
+            tc05::fence_after_sync();
+            issue_pv(i, j);
+            if (j + 1 < ni) { issue_qk(i, j + 1); tc05::mma_commit(bar_s + 8 * i); }
+            else tc05::mma_commit(bar_o + 8 * i);
+          }
+        }
+        tc05::mma_commit(bar_ve + 8 * s);            // V_j and K_{j+1} are consumed by everything issued so far
+        if (more_k) tc05::mma_commit(bar_ke + 8 * (s ^ 1));
+      }
+      // the last commit must have landed in this CTA's shared memory before the CTA may exit
+      mbar_wait(bar_ve + 8 * ((nmax - 1) & 1), ((nmax - 1) >> 1) & 1);
+    }
+  } else if (warp >= 10) {
+    // register donors: 384 threads x 168 registers is the CTA's pool; four warps at 40 leave 232 for the rest
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
+  } else {
+    // ===================== softmax groups =====================
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 232;");
+    const int grp = warp >> 2;                      // 0: tile A, 1: tile B
+    const int ni = grp ? nB : nA;
+    const int r = tid & 127;                        // row inside the tile
+    const int qi0 = q0 + 128 * grp;                 // first row of this tile inside the prompt
+    const uint32_t lane_base = tmem + (static_cast<uint32_t>((warp & 3) * 32) << 16);
+    const uint32_t tS = lane_base + kTmS + 128 * grp, tO = lane_base + kTmO + 128 * grp;
+    const bool dump = p.dbg && blockIdx.x == 0 && blockIdx.y == 0 && grp == 0;
+    float m_run = -CUDART_INF_F, l_run = 0.f;
+    for (int j = 0; j < ni; ++j) {
+      mbar_wait(bar_s + 8 * grp, j & 1);
+      tc05::fence_after_sync();
+      uint32_t s[4][32];
+#pragma unroll
+      for (int c = 0; c < 4; ++c) tc05::tmem_ld32(tS + c * 32, s[c]);
+      tc05::tmem_wait_ld();
+      if (dump && j == 0) {
+#pragma unroll
+        for (int c = 0; c < 4; ++c)
+#pragma unroll
+          for (int i = 0; i < 32; ++i) p.dbg[r * 128 + c * 32 + i] = __uint_as_float(s[c][i]);
+      }
+      const bool diag = j == ni - 1;                // the only tile that needs masking
+      const int lim = min(r, len - 1 - qi0);        // last valid column of this row in the diagonal tile
+      float mx = -CUDART_INF_F;
+#pragma unroll
+      for (int c = 0; c < 4; ++c)
+#pragma unroll
+        for (int i = 0; i < 32; ++i) {
+          float v = __uint_as_float(s[c][i]) * p.scale_log2;
+          if (diag && c * 32 + i > lim) v = -CUDART_INF_F;
+          s[c][i] = __float_as_uint(v);
+          mx = fmaxf(mx, v);
+        }
+      const float m_new = fmaxf(m_run, mx);
+      const float m_use = m_new == -CUDART_INF_F ? 0.f : m_new;   // row with nothing valid (beyond len)
+      const float alpha = ex2(m_run - m_use);
+      // S_j ready implies the previous P.V of this tile has completed (in-order tensor pipe), so O_i is quiescent
+      if (j > 0 && __any_sync(0xffffffffu, alpha != 1.f)) {
+#pragma unroll
+        for (int c = 0; c < DP / 32; ++c) {
+          uint32_t o[32];
+          tc05::tmem_ld32(tO + c * 32, o);
+          tc05::tmem_wait_ld();
+#pragma unroll
+          for (int i = 0; i < 32; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
+          tc05::tmem_st32(tO + c * 32, o);
+        }
+      }
+      float sum = 0.f;
+#pragma unroll
+      for (int c2 = 0; c2 < 2; ++c2) {
+        uint32_t pk[32];
+#pragma unroll
+        for (int h = 0; h < 2; ++h)
+#pragma unroll
+          for (int i = 0; i < 32; i += 2) {
+            const float p0 = ex2(__uint_as_float(s[c2 * 2 + h][i]) - m_use);
+            const float p1 = ex2(__uint_as_float(s[c2 * 2 + h][i + 1]) - m_use);
+            sum += p0 + p1;
+            pk[h * 16 + (i >> 1)] = pack2<T>(p0, p1);
+          }
+        tc05::tmem_st32(tS + c2 * 32, pk);
+      }
+      l_run = l_run * alpha + sum;
+      m_run = m_new;
+      tc05::tmem_wait_st();
+      tc05::fence_before_sync();
+      mbar_arrive(bar_p + 8 * grp);
+    }
+    if (ni > 0) {
+      // ---- epilogue: O / l -> out ---------------------------------------------------------
+      mbar_wait(bar_o + 8 * grp, 0);
+      tc05::fence_after_sync();
+      const int D = p.head_size;
+      const bool row_ok = qi0 + r < len;
+      const float inv = 1.f / l_run;
+      char* orow = reinterpret_cast<char*>(p.out) +
+                   ((static_cast<int64_t>(tok0) + qi0 + r) * p.out_stride + static_cast<int64_t>(head) * D) * 2;
+#pragma unroll
+      for (int c = 0; c < DP / 32; ++c) {
+        uint32_t o[32];
+        tc05::tmem_ld32(tO + c * 32, o);
+        tc05::tmem_wait_ld();
+        if (dump) {
+#pragma unroll
+          for (int i = 0; i < 32; ++i) p.dbg[128 * 128 + r * DP + c * 32 + i] = __uint_as_float(o[i]);
+          if (c == 0) { p.dbg[128 * 128 + 128 * DP + r] = l_run; p.dbg[128 * 128 + 128 * DP + 128 + r] = m_run; }
+        }
+        if (row_ok) {
+#pragma unroll
+          for (int v = 0; v < 4; ++v) {               // 8 elements = 16 bytes per store
+            if (c * 32 + v * 8 < D) {
+              uint4 w;
+              w.x = pack2<T>(__uint_as_float(o[v * 8 + 0]) * inv, __uint_as_float(o[v * 8 + 1]) * inv);
+              w.y = pack2<T>(__uint_as_float(o[v * 8 + 2]) * inv, __uint_as_float(o[v * 8 + 3]) * inv);
+              w.z = pack2<T>(__uint_as_float(o[v * 8 + 4]) * inv, __uint_as_float(o[v * 8 + 5]) * inv);
+              w.w = pack2<T>(__uint_as_float(o[v * 8 + 6]) * inv, __uint_as_float(o[v * 8 + 7]) * inv);
+              *reinterpret_cast<uint4*>(orow + (c * 32 + v * 8) * 2) = w;
+            }
+          }
+        }
+      }
+    }
+  }
+  tc05::fence_before_sync();
+  __syncthreads();
+  if (warp == 0) tc05::tmem_free<kTmCols>(tmem);
+}
+
+}  // namespace pa
