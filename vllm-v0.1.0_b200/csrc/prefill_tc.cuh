@@ -46,6 +46,24 @@ __device__ __forceinline__ float ex2(float x) {   // exp2(-inf) == 0
   return y;
 }
 
+__device__ __forceinline__ float max3(float a, float b, float c) {   // FMNMX3
+  float d;
+  asm("max.f32 %0, %1, %2, %3;" : "=f"(d) : "f"(a), "f"(b), "f"(c));
+  return d;
+}
+// (d0, d1) = (a0, a1) * b + c on the packed fp32 pipe (FFMA2)
+__device__ __forceinline__ void ffma2(float& d0, float& d1, float a0, float a1, float b, float c) {
+  asm("{.reg .b64 ra, rb, rc, rd;\n\tmov.b64 ra, {%2, %3};\n\tmov.b64 rb, {%4, %4};\n\tmov.b64 rc, {%5, %5};\n\t"
+      "fma.rn.f32x2 rd, ra, rb, rc;\n\tmov.b64 {%0, %1}, rd;}"
+      : "=f"(d0), "=f"(d1) : "f"(a0), "f"(a1), "f"(b), "f"(c));
+}
+// (a0, a1) += (b0, b1) (FADD2)
+__device__ __forceinline__ void fadd2(float& a0, float& a1, float b0, float b1) {
+  asm("{.reg .b64 ra, rb;\n\tmov.b64 ra, {%0, %1};\n\tmov.b64 rb, {%2, %3};\n\tadd.rn.f32x2 ra, ra, rb;\n\t"
+      "mov.b64 {%0, %1}, ra;}"
+      : "+f"(a0), "+f"(a1) : "f"(b0), "f"(b1));
+}
+
 template <typename T, int DP>
 __global__ void __launch_bounds__(kPfThreads, 1)
 prefill_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant__ CUtensorMap tmk,
@@ -56,7 +74,10 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant
   constexpr uint32_t kTileBytes = kAtoms * kAtomBytes;
   constexpr bool kBf16 = T::kId == PA_BF16;
   constexpr uint32_t kIdescQK = tc05::instr_desc_f16(kBf16, 128, 128, false, false);
-  constexpr uint32_t kIdescPV = tc05::instr_desc_f16(kBf16, 128, DP, false, true);
+  // head sizes 80 and 96 ride in the 128-wide tiles (TMA zero-fills the padding) but only their own
+  // k-steps of Q.K^T and their own N columns of P.V are issued
+  const uint32_t idesc_pv = tc05::instr_desc_f16(kBf16, 128, p.head_size, false, true);
+  const int qk_steps = p.head_size / 16;
   constexpr uint32_t kTmS = 0, kTmO = 256, kTmCols = 512;   // S_i at 128 i, O_i at 256 + 128 i
 
   extern __shared__ unsigned char smem_raw[];
@@ -97,7 +118,7 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant
 
   if (warp == 8) {
     // ===================== TMA producer =====================
-    asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 56;");
     if (lane == 0) {
       auto load_tile = [&](const CUtensorMap* map, uint32_t dst, int row0, uint32_t bar) {
 #pragma unroll
@@ -119,12 +140,13 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant
     }
   } else if (warp == 9) {
     // ===================== MMA issuer =====================
-    asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 56;");
     if (lane == 0) {
       auto issue_qk = [&](int i, int j) {           // S_i = Q_i . K_j^T
         const uint32_t qb = sQ + i * kTileBytes, kb = sK + (j & 1) * kTileBytes;
 #pragma unroll
         for (int kk = 0; kk < DP / 16; ++kk) {
+          if (kk >= qk_steps) break;
           const uint32_t off = (kk >> 2) * kAtomBytes + (kk & 3) * 32;
           tc05::mma_ss(tmem + kTmS + 128 * i, tc05::smem_desc_sw128(qb + off, 16, 1024),
                        tc05::smem_desc_sw128(kb + off, 16, 1024), kIdescQK, kk > 0);
@@ -135,7 +157,7 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant
 #pragma unroll
         for (int kk = 0; kk < kPfCols / 16; ++kk)
           tc05::mma_ts(tmem + kTmO + 128 * i, tmem + kTmS + 128 * i + kk * 8,
-                       tc05::smem_desc_sw128(vb + kk * 2048, kAtomBytes, 1024), kIdescPV, j > 0 || kk > 0);
+                       tc05::smem_desc_sw128(vb + kk * 2048, kAtomBytes, 1024), idesc_pv, j > 0 || kk > 0);
       };
       mbar_wait(bar_q, 0);
       mbar_wait(bar_kf, 0);
@@ -167,11 +189,12 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant
       mbar_wait(bar_ve + 8 * ((nmax - 1) & 1), ((nmax - 1) >> 1) & 1);
     }
   } else if (warp >= 10) {
-    // register donors: 384 threads x 168 registers is the CTA's pool; four warps at 40 leave 232 for the rest
-    asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
+    // register donors.  384 threads x 168 registers is the CTA's pool = 128 x 56 + 256 x 224; setmaxnreg must be
+    // the same instruction in all four warps of a warpgroup (warps 8-11), whatever branch they sit in
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 56;");
   } else {
     // ===================== softmax groups =====================
-    asm volatile("setmaxnreg.inc.sync.aligned.u32 232;");
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 224;");
     const int grp = warp >> 2;                      // 0: tile A, 1: tile B
     const int ni = grp ? nB : nA;
     const int r = tid & 127;                        // row inside the tile
@@ -193,34 +216,46 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant
 #pragma unroll
           for (int i = 0; i < 32; ++i) p.dbg[r * 128 + c * 32 + i] = __uint_as_float(s[c][i]);
       }
-      const bool diag = j == ni - 1;                // the only tile that needs masking
-      const int lim = min(r, len - 1 - qi0);        // last valid column of this row in the diagonal tile
-      float mx = -CUDART_INF_F;
+      if (j == ni - 1) {                            // the diagonal tile is the only one that needs masking
+        const int lim = min(r, len - 1 - qi0);      // last valid column of this row
 #pragma unroll
-      for (int c = 0; c < 4; ++c)
+        for (int c = 0; c < 4; ++c)
 #pragma unroll
-        for (int i = 0; i < 32; ++i) {
-          float v = __uint_as_float(s[c][i]) * p.scale_log2;
-          if (diag && c * 32 + i > lim) v = -CUDART_INF_F;
-          s[c][i] = __float_as_uint(v);
-          mx = fmaxf(mx, v);
-        }
-      const float m_new = fmaxf(m_run, mx);
-      const float m_use = m_new == -CUDART_INF_F ? 0.f : m_new;   // row with nothing valid (beyond len)
-      const float alpha = ex2(m_run - m_use);
-      // S_j ready implies the previous P.V of this tile has completed (in-order tensor pipe), so O_i is quiescent
-      if (j > 0 && __any_sync(0xffffffffu, alpha != 1.f)) {
+          for (int i = 0; i < 32; ++i)
+            if (c * 32 + i > lim) s[c][i] = 0xff800000u;   // -inf
+      }
+      // row maximum of the raw logits (scale > 0), four independent chains of 3-input max
+      float mx[4];
 #pragma unroll
-        for (int c = 0; c < DP / 32; ++c) {
-          uint32_t o[32];
-          tc05::tmem_ld32(tO + c * 32, o);
-          tc05::tmem_wait_ld();
+      for (int c = 0; c < 4; ++c) {
+        mx[c] = max3(__uint_as_float(s[c][0]), __uint_as_float(s[c][1]), __uint_as_float(s[c][2]));
 #pragma unroll
-          for (int i = 0; i < 32; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
-          tc05::tmem_st32(tO + c * 32, o);
+        for (int i = 3; i + 1 < 32; i += 2) mx[c] = max3(mx[c], __uint_as_float(s[c][i]), __uint_as_float(s[c][i + 1]));
+        mx[c] = fmaxf(mx[c], __uint_as_float(s[c][31]));
+      }
+      const float m_tile = fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3])) * p.scale_log2;
+      // Lazy rescaling: the reference maximum only moves when the row maximum grew by more than 2^8; until then
+      // probabilities may exceed 1 (by at most 2^8), which fp32 sums and 16-bit P hold without loss, and
+      // O / l is unchanged because both carry the same reference.  O_i is quiescent here: S_j ready implies
+      // the previous P.V of this tile completed (in-order tensor pipe).
+      const bool move = m_tile > m_run + 8.f;       // always true on the first tile (m_run = -inf)
+      if (__any_sync(0xffffffffu, move)) {
+        const float alpha = move ? ex2(m_run - m_tile) : 1.f;
+        if (move) { m_run = m_tile; l_run *= alpha; }
+        if (j > 0) {
+#pragma unroll
+          for (int c = 0; c < DP / 32; ++c) {
+            uint32_t o[32];
+            tc05::tmem_ld32(tO + c * 32, o);
+            tc05::tmem_wait_ld();
+#pragma unroll
+            for (int i = 0; i < 32; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
+            tc05::tmem_st32(tO + c * 32, o);
+          }
         }
       }
-      float sum = 0.f;
+      const float neg_m = -m_run;
+      float sum[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
       for (int c2 = 0; c2 < 2; ++c2) {
         uint32_t pk[32];
@@ -228,15 +263,15 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant
         for (int h = 0; h < 2; ++h)
 #pragma unroll
           for (int i = 0; i < 32; i += 2) {
-            const float p0 = ex2(__uint_as_float(s[c2 * 2 + h][i]) - m_use);
-            const float p1 = ex2(__uint_as_float(s[c2 * 2 + h][i + 1]) - m_use);
-            sum += p0 + p1;
+            float a0, a1;
+            ffma2(a0, a1, __uint_as_float(s[c2 * 2 + h][i]), __uint_as_float(s[c2 * 2 + h][i + 1]), p.scale_log2, neg_m);
+            const float p0 = ex2(a0), p1 = ex2(a1);
+            fadd2(sum[(i >> 1) & 1 ? 2 : 0], sum[(i >> 1) & 1 ? 3 : 1], p0, p1);
             pk[h * 16 + (i >> 1)] = pack2<T>(p0, p1);
           }
         tc05::tmem_st32(tS + c2 * 32, pk);
       }
-      l_run = l_run * alpha + sum;
-      m_run = m_new;
+      l_run += (sum[0] + sum[1]) + (sum[2] + sum[3]);
       tc05::tmem_wait_st();
       tc05::fence_before_sync();
       mbar_arrive(bar_p + 8 * grp);
