@@ -322,6 +322,46 @@ PA_API int pa_swap_blocks_ex(const void* src, void* dst, int64_t block_bytes,
                       int64_t num_blocks, int32_t kind, int32_t engine,
                       void* stream);
 
+/* ------------------------------------------------------------------------ */
+/* all-reduce of the row-parallel output that follows attention             */
+/* ------------------------------------------------------------------------ */
+
+/*
+ * replaces: GraphAllReduce.launch
+ *           vllm/model_executor/parallel_utils/parallel_state.py:506-556 (NCCL
+ *           all_reduce replayed from a CUDA graph), called after every
+ *           RowParallelLinear (tensor_parallel/layers.py:419-426) -- the one
+ *           collective next to the attention path (head-sharded attention itself
+ *           needs none).
+ *
+ * In-place sum over `world` ranks of numel elements starting offset_bytes into
+ * every rank's buffer; all ranks end up with identical bits.  One kernel per
+ * rank over NVLink peer memory: rank r reduces slice r (multimem.ld_reduce in
+ * the NVSwitch when multicast_ptr is given, else 16-byte peer loads summed in
+ * fp32 in rank order) and writes the sum to every rank (multimem.st / peer
+ * stores), between two flag barriers.  Stream-ordered, no host synchronisation,
+ * capturable in a CUDA graph.
+ *   peer_buffers  HOST array [world]: this buffer's address on every rank, mapped
+ *                 into the calling process (symmetric memory); [rank] is local
+ *   peer_flags    HOST array [world]: pa_allreduce_flag_bytes() bytes on every
+ *                 rank, zeroed once before first use (they return to zero)
+ *   multicast_ptr multicast mapping of the buffer (NVLS) or NULL
+ * All ranks must call with the same offset / numel / dtype.  numel * sizeof(T)
+ * and offset_bytes must be multiples of 16; world <= 8.
+ */
+PA_API int pa_allreduce(void* const* peer_buffers, void* const* peer_flags,
+                 void* multicast_ptr, int64_t offset_bytes, int64_t numel,
+                 int32_t rank, int32_t world, int32_t dtype, void* stream);
+
+PA_API int pa_allreduce_flag_bytes(void);
+
+/* The peer path with all `world` ranks inside ONE launch on ONE device
+ * (buffers[r] / flags[r] are ordinary device allocations): how the kernel is
+ * tested where only one GPU is present.  Tests only. */
+PA_API int pa_allreduce_emulated(void* const* buffers, void* const* flags,
+                          int64_t offset_bytes, int64_t numel, int32_t world,
+                          int32_t dtype, void* stream);
+
 #ifdef __cplusplus
 } /* extern "C" */
 #endif

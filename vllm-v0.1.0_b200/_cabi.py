@@ -53,6 +53,9 @@ SIGNATURES = {
     "pa_rotary_embedding_neox": (C.c_int, [_vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _i64, _i64, _i32, _vp]),
     "pa_rope_reshape_and_cache": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _i32, _i32,
                                             _i64, _i64, _i64, _i32, _vp]),
+    "pa_allreduce": (C.c_int, [C.POINTER(_vp), C.POINTER(_vp), _vp, _i64, _i64, _i32, _i32, _i32, _vp]),
+    "pa_allreduce_flag_bytes": (C.c_int, []),
+    "pa_allreduce_emulated": (C.c_int, [C.POINTER(_vp), C.POINTER(_vp), _i64, _i64, _i32, _i32, _vp]),
     "pa_copy_blocks": (C.c_int, [C.POINTER(_vp), C.POINTER(_vp), _i32, C.POINTER(_i64), _i64, _i64, _vp]),
     "pa_swap_blocks": (C.c_int, [_vp, _vp, _i64, C.POINTER(_i64), C.POINTER(_i64), _i64, _i32, _vp]),
     "pa_swap_blocks_ex": (C.c_int, [_vp, _vp, _i64, C.POINTER(_i64), C.POINTER(_i64), _i64, _i32, _i32, _vp]),
