@@ -21,7 +21,7 @@ def _oracle_sum(bufs):
 def test_allreduce_symbols_and_argument_checks():
     from vllm_b200 import _cabi
     lib = _cabi.lib()
-    assert lib.pa_allreduce_flag_bytes() >= 64 * 8 * 4
+    assert lib.pa_allreduce_flag_bytes() >= 128 * 8 * 4
     one = (C.c_void_p * 1)(None)
     assert lib.pa_allreduce(one, one, None, 0, 16, 0, 9, _cabi.PA_F16, None) == _cabi.PA_ERR_INVALID_ARGUMENT
     assert lib.pa_allreduce(one, one, None, 0, 16, 3, 2, _cabi.PA_F16, None) == _cabi.PA_ERR_INVALID_ARGUMENT

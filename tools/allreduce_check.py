@@ -34,6 +34,39 @@ def time_fn(fn, iters=200, warmup=20):
     return float(t.item())
 
 
+def graph_time_us(fn, per_graph=20, replays=10):
+    """Device time per call: `per_graph` calls captured in one CUDA graph (no host launch cost in the
+    number; also shows the call is capturable), replayed `replays` times; max over ranks."""
+    fn()
+    torch.cuda.synchronize()
+    dist.barrier()
+    s = torch.cuda.Stream()
+    s.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(s):
+        for _ in range(3):
+            fn()
+    torch.cuda.current_stream().wait_stream(s)
+    torch.cuda.synchronize()
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        for _ in range(per_graph):
+            fn()
+    torch.cuda.synchronize()
+    dist.barrier()
+    g.replay()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    dist.barrier()
+    e0.record()
+    for _ in range(replays):
+        g.replay()
+    e1.record()
+    torch.cuda.synchronize()
+    t = torch.tensor([e0.elapsed_time(e1) * 1e3 / (per_graph * replays)], device="cuda", dtype=torch.float64)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item())
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--json", default=os.path.join(ROOT, "gpurun_out", "allreduce_check.json"))
@@ -78,8 +111,8 @@ def main():
                     flag = torch.tensor([int(ok and same)], device="cuda")
                     dist.all_reduce(flag, op=dist.ReduceOp.MIN)
                     ok_all = ok_all and bool(flag.item())
-                us_ours = time_fn(lambda: ar.launch(x)) * 1e3
-                us_nccl = time_fn(lambda: dist.all_reduce(x)) * 1e3
+                us_ours = graph_time_us(lambda: ar.launch(x))
+                us_nccl = graph_time_us(lambda: dist.all_reduce(x))
                 if rank == 0:
                     nbytes = tokens * hidden * x.element_size()
                     row = {"dtype": str(dtype).split(".")[-1], "multimem": mm, "tokens": tokens, "bytes": nbytes,

@@ -22,7 +22,7 @@
 namespace pa {
 
 constexpr int kArMaxWorld = 8;
-constexpr int kArMaxBlocks = 64;
+constexpr int kArMaxBlocks = 128;
 
 struct ArParams {
   void* bufs[kArMaxWorld];        // every rank's buffer (same offset applied already), peer-mapped
@@ -115,23 +115,41 @@ allreduce_kernel(const ArParams p) {
   const int64_t begin = per * rank;
   const int64_t end = begin + per < p.nvec ? begin + per : p.nvec;
   const int64_t step = static_cast<int64_t>(gridDim.x) * blockDim.x;
-  for (int64_t v = begin + static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; v < end; v += step) {
+  constexpr int kU = 4;   // independent 16-byte vectors in flight per thread
+  for (int64_t v0 = begin + static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; v0 < end; v0 += kU * step) {
     if constexpr (kMultimem) {
-      char* addr = static_cast<char*>(p.mc) + v * 16;
-      multimem_st(addr, multimem_ld_reduce<T>(addr));
+      uint4 val[kU];
+#pragma unroll
+      for (int u = 0; u < kU; ++u)
+        if (v0 + u * step < end) val[u] = multimem_ld_reduce<T>(static_cast<char*>(p.mc) + (v0 + u * step) * 16);
+#pragma unroll
+      for (int u = 0; u < kU; ++u)
+        if (v0 + u * step < end) multimem_st(static_cast<char*>(p.mc) + (v0 + u * step) * 16, val[u]);
     } else {
-      float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-      uint4 in[kArMaxWorld];
 #pragma unroll
-      for (int r = 0; r < kArMaxWorld; ++r)
-        if (r < p.world) in[r] = ld_peer(static_cast<const char*>(p.bufs[r]) + v * 16);
+      for (int u0 = 0; u0 < kU; u0 += 2) {          // two vectors x world loads in flight
+        uint4 in[2][kArMaxWorld];
 #pragma unroll
-      for (int r = 0; r < kArMaxWorld; ++r)
-        if (r < p.world) accumulate<T>(acc, in[r]);
-      const uint4 out = finish<T>(acc);
+        for (int u = 0; u < 2; ++u)
 #pragma unroll
-      for (int r = 0; r < kArMaxWorld; ++r)
-        if (r < p.world) *reinterpret_cast<uint4*>(static_cast<char*>(p.bufs[r]) + v * 16) = out;
+          for (int r = 0; r < kArMaxWorld; ++r)
+            if (r < p.world && v0 + (u0 + u) * step < end)
+              in[u][r] = ld_peer(static_cast<const char*>(p.bufs[r]) + (v0 + (u0 + u) * step) * 16);
+#pragma unroll
+        for (int u = 0; u < 2; ++u) {
+          const int64_t v = v0 + (u0 + u) * step;
+          if (v < end) {
+            float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+            for (int r = 0; r < kArMaxWorld; ++r)
+              if (r < p.world) accumulate<T>(acc, in[u][r]);
+            const uint4 out = finish<T>(acc);
+#pragma unroll
+            for (int r = 0; r < kArMaxWorld; ++r)
+              if (r < p.world) *reinterpret_cast<uint4*>(static_cast<char*>(p.bufs[r]) + v * 16) = out;
+          }
+        }
+      }
     }
   }
   ar_barrier(p, rank);
@@ -172,7 +190,7 @@ static int allreduce(void* const* bufs, void* const* flags, void* multicast, int
   p.world = world;
   // one 16-byte vector per thread and pass; every block must be resident at once (they meet at the barriers)
   const int64_t per = (p.nvec + world - 1) / world;
-  int blocks = static_cast<int>((per + 511) / 512);
+  int blocks = static_cast<int>((per + 2047) / 2048);   // 4 vectors per thread and pass
   const int cap = emulate ? 16 : kArMaxBlocks;
   if (blocks > cap) blocks = cap;
   if (blocks < 1) blocks = 1;
