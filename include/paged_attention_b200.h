@@ -63,7 +63,8 @@ enum pa_status {
   PA_ERR_UNSUPPORTED_BLOCK_SIZE = -2, /* block_size not in {8, 16, 32}       */
   PA_ERR_UNSUPPORTED_DTYPE = -3,
   PA_ERR_INVALID_ARGUMENT = -4, /* NULL pointer, negative size, misalignment */
-  PA_ERR_CUDA = -5              /* a CUDA runtime call failed                */
+  PA_ERR_CUDA = -5,             /* a CUDA runtime call failed                */
+  PA_ERR_NEED_TABLE = -6        /* pa_step_prepare_inputs: a sequence needs its full block table */
 };
 
 /* ------------------------------------------------------------------------ */
@@ -361,6 +362,94 @@ PA_API int pa_allreduce_flag_bytes(void);
 PA_API int pa_allreduce_emulated(void* const* buffers, void* const* flags,
                           int64_t offset_bytes, int64_t numel, int32_t world,
                           int32_t dtype, void* stream);
+
+/* ------------------------------------------------------------------------ */
+/* per-step inputs: device-resident block tables                            */
+/* ------------------------------------------------------------------------ */
+
+/*
+ * replaces: Worker._prepare_inputs, vllm/worker/worker.py:128-237 (with
+ *           _pad_to_alignment / _pad_to_max, :304-309) -- the producer of
+ *           InputMetadata's tensors (vllm/model_executor/input_metadata.py:10-40).
+ *
+ * The reference rebuilds every block table as nested Python lists each step and
+ * uploads tokens, positions, slot mapping, context lengths and the padded
+ * [S, MB] table with five blocking pageable copies.  Here the block tables LIVE
+ * on the device in a pa_step_state; a step sends only what changed (the block a
+ * sequence appended or copy-on-wrote, full tables only for sequences that were
+ * not in the previous step) in ONE pinned, stream-ordered copy, and ONE kernel
+ * patches the resident tables and writes all five tensors exactly as the
+ * reference lays them out:
+ *   tokens / positions  int64 [pad8(num_prompt_tokens + S)]: prompt tokens of all
+ *                       prompts, then one token per generation sequence, then
+ *                       zeros up to a multiple of 8 (worker.py:201-204)
+ *   slot_mapping        int32 [num_prompt_tokens + S]: table[pos / B] * B + pos % B
+ *   context_lens        int32 [S]
+ *   block_tables        int32 [S, width], rows zero-padded (worker.py:211-214)
+ * Bit-identical to the reference's tensors (tests/golden/step_inputs_trace.json.gz).
+ *
+ * A state belongs to one worker thread; calls on it must not overlap.  Work is
+ * enqueued on `stream`; the host arrays may be reused as soon as the call
+ * returns (they are packed into the state's pinned staging ring).
+ */
+typedef struct pa_step_state pa_step_state;
+
+PA_API int pa_step_state_create(int32_t max_seqs, int32_t max_blocks_per_seq,
+                         int32_t block_size, pa_step_state** state_out);
+PA_API int pa_step_state_destroy(pa_step_state* state);
+/* Forgets every sequence (the next step must bring full tables). */
+PA_API int pa_step_state_reset(pa_step_state* state);
+
+typedef struct pa_step_batch {
+  /* generation sequences, in batch order (worker.py:170-199) */
+  int32_t num_seqs;
+  const int64_t* seq_ids;       /* [S] scheduler sequence ids (unique in a step)      */
+  const int64_t* last_tokens;   /* [S] seq_data.get_last_token_id()                   */
+  const int32_t* context_lens;  /* [S] seq_data.get_len()                             */
+  const int32_t* num_blocks;    /* [S] len(block_table)                               */
+  const int32_t* last_block;    /* [S] block_table[-1]                                */
+  /* Full tables (CSR), for the sequences that bring one: table_offsets[i+1] -
+   * table_offsets[i] is 0 or num_blocks[i].  NULL = nobody brings one.  Required
+   * for a sequence that was not in the previous step; a sequence that was may
+   * omit it if its table only grew by one block or had its last block replaced
+   * (BlockSpaceManager.append_slot, core/block_manager.py:111-135) -- anything
+   * else (beam-search forks, block_manager.py:137-143) must bring the table,
+   * which is diffed against the resident copy and only the changed span is sent. */
+  const int64_t* table_offsets; /* [S + 1] or NULL */
+  const int32_t* table_blocks;
+  /* prompts, in batch order (worker.py:138-167) */
+  int32_t num_prompts;
+  const int64_t* prompt_offsets;        /* [P + 1] into prompt_tokens                 */
+  const int64_t* prompt_tokens;
+  const int64_t* prompt_table_offsets;  /* [P + 1] into prompt_table_blocks; an empty */
+  const int32_t* prompt_table_blocks;   /* row = "block tables not initialised yet":  */
+                                        /* dummy slot 0 (worker.py:160-164)           */
+} pa_step_batch;
+
+typedef struct pa_step_outputs {  /* DEVICE pointers, caller-allocated */
+  int64_t* tokens;        /* [pad8(num_prompt_tokens + S)] */
+  int64_t* positions;     /* same length */
+  int32_t* slot_mapping;  /* [num_prompt_tokens + S] */
+  int32_t* context_lens;  /* [S] */
+  int32_t* block_tables;  /* [S, block_table_width] */
+  int32_t block_table_width; /* >= max(num_blocks); the reference uses == */
+} pa_step_outputs;
+
+typedef struct pa_step_info {
+  int32_t max_context_len;  /* worker.py:191 */
+  int32_t max_num_blocks;   /* max(num_blocks), worker.py:192-193 */
+  int32_t num_tokens;       /* num_prompt_tokens + S (before padding) */
+  int32_t num_incremental;  /* sequences updated without a full table */
+  int32_t num_full;         /* sequences whose table was sent whole */
+  int32_t num_diffed;       /* sequences that brought a table of which only a span was sent */
+  int64_t h2d_bytes;        /* bytes of the one host->device copy of this step */
+} pa_step_info;
+
+/* On PA_ERR_NEED_TABLE the state is unchanged and need_table[i] (optional, [S])
+ * is 1 for every sequence that must bring its full table; call again. */
+PA_API int pa_step_prepare_inputs(pa_step_state* state, const pa_step_batch* batch,
+                           const pa_step_outputs* out, pa_step_info* info,
+                           uint8_t* need_table, void* stream);
 
 #ifdef __cplusplus
 } /* extern "C" */

@@ -10,6 +10,7 @@ from .cache_engine import CacheEngine, kv_cache_shapes  # noqa: F401
 from . import sharding  # noqa: F401
 from .input_metadata import BlockDiagonalCausalMask, InputMetadata  # noqa: F401
 from .paged_attention import PagedAttention, PagedAttentionWithRoPE  # noqa: F401
+from .step_inputs import StepInputs  # noqa: F401
 
 __all__ = ["attention_ops", "cache_ops", "pos_encoding_ops", "CacheEngine", "kv_cache_shapes", "InputMetadata",
-           "BlockDiagonalCausalMask", "PagedAttention", "PagedAttentionWithRoPE"]
+           "BlockDiagonalCausalMask", "PagedAttention", "PagedAttentionWithRoPE", "StepInputs"]

@@ -21,6 +21,7 @@ PA_ERR_UNSUPPORTED_BLOCK_SIZE = -2
 PA_ERR_UNSUPPORTED_DTYPE = -3
 PA_ERR_INVALID_ARGUMENT = -4
 PA_ERR_CUDA = -5
+PA_ERR_NEED_TABLE = -6
 
 
 class DecodeTuning(C.Structure):
@@ -30,6 +31,27 @@ class DecodeTuning(C.Structure):
 
 
 _vp, _i32, _i64, _f32 = C.c_void_p, C.c_int32, C.c_int64, C.c_float
+
+
+class StepBatch(C.Structure):
+    """Mirror of `pa_step_batch` (host arrays of one step)."""
+    _fields_ = [("num_seqs", _i32), ("seq_ids", _vp), ("last_tokens", _vp), ("context_lens", _vp),
+                ("num_blocks", _vp), ("last_block", _vp), ("table_offsets", _vp), ("table_blocks", _vp),
+                ("num_prompts", _i32), ("prompt_offsets", _vp), ("prompt_tokens", _vp),
+                ("prompt_table_offsets", _vp), ("prompt_table_blocks", _vp)]
+
+
+class StepOutputs(C.Structure):
+    """Mirror of `pa_step_outputs` (device pointers)."""
+    _fields_ = [("tokens", _vp), ("positions", _vp), ("slot_mapping", _vp), ("context_lens", _vp),
+                ("block_tables", _vp), ("block_table_width", _i32)]
+
+
+class StepInfo(C.Structure):
+    """Mirror of `pa_step_info`."""
+    _fields_ = [("max_context_len", _i32), ("max_num_blocks", _i32), ("num_tokens", _i32),
+                ("num_incremental", _i32), ("num_full", _i32), ("num_diffed", _i32), ("h2d_bytes", _i64)]
+
 
 # name -> (restype, argtypes); must list every PA_API symbol of the header
 SIGNATURES = {
@@ -56,6 +78,11 @@ SIGNATURES = {
     "pa_allreduce": (C.c_int, [C.POINTER(_vp), C.POINTER(_vp), _vp, _i64, _i64, _i32, _i32, _i32, _vp]),
     "pa_allreduce_flag_bytes": (C.c_int, []),
     "pa_allreduce_emulated": (C.c_int, [C.POINTER(_vp), C.POINTER(_vp), _i64, _i64, _i32, _i32, _vp]),
+    "pa_step_state_create": (C.c_int, [_i32, _i32, _i32, C.POINTER(_vp)]),
+    "pa_step_state_destroy": (C.c_int, [_vp]),
+    "pa_step_state_reset": (C.c_int, [_vp]),
+    "pa_step_prepare_inputs": (C.c_int, [_vp, C.POINTER(StepBatch), C.POINTER(StepOutputs), C.POINTER(StepInfo),
+                                         _vp, _vp]),
     "pa_copy_blocks": (C.c_int, [C.POINTER(_vp), C.POINTER(_vp), _i32, C.POINTER(_i64), _i64, _i64, _vp]),
     "pa_swap_blocks": (C.c_int, [_vp, _vp, _i64, C.POINTER(_i64), C.POINTER(_i64), _i64, _i32, _vp]),
     "pa_swap_blocks_ex": (C.c_int, [_vp, _vp, _i64, C.POINTER(_i64), C.POINTER(_i64), _i64, _i32, _i32, _vp]),

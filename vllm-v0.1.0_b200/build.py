@@ -22,7 +22,7 @@ BUILD = os.path.join(HERE, "build")
 LIBDIR = os.path.join(HERE, "lib")
 LIB = os.path.join(LIBDIR, "libpaged_b200.so")
 
-SOURCES = ["pa_api.cu", "cache_movers.cu", "probe.cu", "prefill_attention.cu", "allreduce.cu", "decode_f16.cu", "decode_bf16.cu", "decode_f32.cu"]
+SOURCES = ["pa_api.cu", "cache_movers.cu", "step_tables.cu", "probe.cu", "prefill_attention.cu", "allreduce.cu", "decode_f16.cu", "decode_bf16.cu", "decode_f32.cu"]
 HEADERS = [os.path.join(CSRC, "pa_common.cuh"), os.path.join(CSRC, "decode_attention.cuh"), os.path.join(CSRC, "tc05.cuh"), os.path.join(CSRC, "prefill_tc.cuh"),
            os.path.join(ROOT, "include", "paged_attention_b200.h")]
 
