@@ -65,6 +65,7 @@ def run(name, num_seqs, ctx, block_size, steps, dev):
         t1 = time.perf_counter()
         if step >= 3:
             t_lit.append(reference_literal(groups, block_size, dev)[0])
+        t1b = time.perf_counter()
         e0.record()
         tokens, positions, meta = prep.prepare_inputs(groups)
         e1.record()
@@ -76,7 +77,7 @@ def run(name, num_seqs, ctx, block_size, steps, dev):
             assert torch.equal(want[k], got[k]), (step, k)
         if step >= 3:
             t_ref.append(t1 - t0)
-            t_ours.append(t2 - t1)
+            t_ours.append(t2 - t1b)
             dev_ms.append(e0.elapsed_time(e1))
             ref_bytes.append(sum(v.numel() * v.element_size() for v in want.values()))
             our_bytes.append(prep.last_info.h2d_bytes)

@@ -46,6 +46,13 @@ __device__ __forceinline__ float ex2(float x) {   // exp2(-inf) == 0
   return y;
 }
 
+// the same, pinned between the named barriers of the ping-pong section (volatile asm keeps its order)
+__device__ __forceinline__ float ex2_pinned(float x) {
+  float y;
+  asm volatile("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
 __device__ __forceinline__ float max3(float a, float b, float c) {   // FMNMX3
   float d;
   asm("max.f32 %0, %1, %2, %3;" : "=f"(d) : "f"(a), "f"(b), "f"(c));
@@ -63,6 +70,11 @@ __device__ __forceinline__ void fadd2(float& a0, float& a1, float b0, float b1) 
       "mov.b64 {%0, %1}, ra;}"
       : "+f"(a0), "+f"(a1) : "f"(b0), "f"(b1));
 }
+
+// Named barriers 1 and 2 hand the special-function unit back and forth between the two softmax groups
+// (bar.sync by the 128 threads that wait, bar.arrive by the 128 that release).
+__device__ __forceinline__ void named_sync(int id) { asm volatile("bar.sync %0, 256;" :: "r"(id) : "memory"); }
+__device__ __forceinline__ void named_arrive(int id) { asm volatile("bar.arrive %0, 256;" :: "r"(id) : "memory"); }
 
 template <typename T, int DP>
 __global__ void __launch_bounds__(kPfThreads, 1)
@@ -90,6 +102,7 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant
   const uint32_t bar_kf = sBar + 8, bar_ke = sBar + 24, bar_vf = sBar + 40, bar_ve = sBar + 56;   // [2] each
   const uint32_t bar_s = sBar + 72, bar_p = sBar + 88, bar_o = sBar + 104;                        // [2] each
   const uint32_t tm_slot = sBar + 120;
+  const uint32_t sc_slot = sBar + 124;             // scale_log2, re-read after the ping-pong barrier (see below)
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int head = blockIdx.x;
@@ -107,6 +120,7 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant
       mbar_init(bar_vf + 8 * s, 1); mbar_init(bar_ve + 8 * s, 1);
       mbar_init(bar_s + 8 * s, 1); mbar_init(bar_p + 8 * s, 128); mbar_init(bar_o + 8 * s, 1);
     }
+    asm volatile("st.shared.f32 [%0], %1;" :: "r"(sc_slot), "f"(p.scale_log2) : "memory");
     mbar_init_fence();
   }
   if (warp == 0) { __syncwarp(); tc05::tmem_alloc<kTmCols>(tm_slot); }
@@ -203,6 +217,14 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant
     const uint32_t tS = lane_base + kTmS + 128 * grp, tO = lane_base + kTmO + 128 * grp;
     const bool dump = p.dbg && blockIdx.x == 0 && blockIdx.y == 0 && grp == 0;
     float m_run = -CUDART_INF_F, l_run = 0.f;
+    // The exponentials of a tile keep the SM's special-function unit busy for as long as the tensor core
+    // needs for that tile's two matrix products.  Left alone, the two groups drift into phase -- both in
+    // their exponentials (sharing the unit), then both waiting for the tensor core -- and each unit idles
+    // half of the time.  So the exponential section is a critical section that alternates A, B, A, B, ...:
+    // while one group is in it the tensor core runs the other tile's P.V and next Q.K^T.
+    const bool pingpong = nB > 0;
+    const int bar_mine = 1 + grp, bar_other = 2 - grp;
+    if (pingpong && grp == 1) named_arrive(bar_other);          // A goes first
     for (int j = 0; j < ni; ++j) {
       mbar_wait(bar_s + 8 * grp, j & 1);
       tc05::fence_after_sync();
@@ -256,6 +278,11 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant
       }
       const float neg_m = -m_run;
       float sum[4] = {0.f, 0.f, 0.f, 0.f};
+      if (pingpong && j < nA) named_sync(bar_mine);   // B's extra (diagonal) tile runs after A's last: no turn to wait for
+      // ptxas moves arithmetic (and MUFU) across BAR.SYNC freely; what it cannot move is a value loaded
+      // after the barrier, so the section's multiplier is re-read from shared memory here
+      float sc;
+      asm volatile("ld.volatile.shared.f32 %0, [%1];" : "=f"(sc) : "r"(sc_slot) : "memory");
 #pragma unroll
       for (int c2 = 0; c2 < 2; ++c2) {
         uint32_t pk[32];
@@ -264,13 +291,17 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant
 #pragma unroll
           for (int i = 0; i < 32; i += 2) {
             float a0, a1;
-            ffma2(a0, a1, __uint_as_float(s[c2 * 2 + h][i]), __uint_as_float(s[c2 * 2 + h][i + 1]), p.scale_log2, neg_m);
-            const float p0 = ex2(a0), p1 = ex2(a1);
+            ffma2(a0, a1, __uint_as_float(s[c2 * 2 + h][i]), __uint_as_float(s[c2 * 2 + h][i + 1]), sc, neg_m);
+            const float p0 = ex2_pinned(a0), p1 = ex2_pinned(a1);
             fadd2(sum[(i >> 1) & 1 ? 2 : 0], sum[(i >> 1) & 1 ? 3 : 1], p0, p1);
             pk[h * 16 + (i >> 1)] = pack2<T>(p0, p1);
           }
         tc05::tmem_st32(tS + c2 * 32, pk);
       }
+      // hand over: B after its tile j lets A into tile j + 1 (if A has one); A after tile j lets B into tile j.
+      // Every arrive is matched by exactly one later sync of the other group before the next arrive on the same
+      // barrier can happen (two back-to-back arrives would complete the barrier with nobody waiting).
+      if (pingpong && (grp == 0 || j + 1 < nA)) named_arrive(bar_other);
       l_run += (sum[0] + sum[1]) + (sum[2] + sum[3]);
       tc05::tmem_wait_st();
       tc05::fence_before_sync();
