@@ -209,6 +209,44 @@ PA_API int pa_prefill_attention_debug(void* out, const void* query, const void* 
                                int64_t out_stride, float scale, int32_t dtype,
                                float* debug, void* stream);
 
+/*
+ * Prompt chunks over the paged cache ("multi-query cached-KV attention"): sequence i
+ * has query_lens[i] new tokens whose keys / values already sit in the cache behind
+ * context_lens[i] - query_lens[i] earlier tokens (a cached prefix, or the earlier
+ * chunks of a long prompt); query row r of the sequence attends to cached tokens
+ * 0 .. r + (context_lens[i] - query_lens[i]).
+ *
+ * parity reference: ref_multi_query_cached_kv_attention,
+ *           tests/kernels/test_attention.py:104-156 (the reference tree holds this
+ *           test reference but no kernel for it; the operator name and argument order
+ *           of the Python shim follow attention_ops.single_query_cached_kv_attention,
+ *           csrc/attention.cpp:3-19)
+ *
+ * query / out: [sum(query_lens)][num_heads][head_size] with token strides q_stride /
+ * out_stride (elements), rows 16-byte aligned.  key_cache / value_cache / block_tables
+ * (DEVICE, int32 [num_seqs][max_num_blocks_per_seq]) as for pa_decode_attention.
+ * query_lens and context_lens are HOST arrays (the reference keeps cu_query_lens as a
+ * Python list).  head_size in {64, 80, 96, 128}, block_size in {8, 16, 32}.
+ * workspace: DEVICE scratch, 256-byte aligned, at least
+ * pa_multi_query_cached_kv_workspace_bytes(sum(context_lens), ...) bytes, owned by the
+ * caller and free for reuse once the stream has passed this call.
+ * Launches: slot generation, one page gather, the prompt-attention kernel.
+ */
+PA_API int64_t pa_multi_query_cached_kv_workspace_bytes(int64_t total_context_tokens,
+                                                 int32_t num_heads, int32_t head_size,
+                                                 int32_t dtype);
+
+PA_API int pa_multi_query_cached_kv_attention(void* out, const void* query,
+                                       const void* key_cache, const void* value_cache,
+                                       float scale, const int32_t* block_tables,
+                                       const int32_t* query_lens,
+                                       const int32_t* context_lens, int32_t num_seqs,
+                                       int32_t num_heads, int32_t head_size,
+                                       int32_t block_size, int32_t max_num_blocks_per_seq,
+                                       int64_t q_stride, int64_t out_stride, int32_t dtype,
+                                       void* workspace, int64_t workspace_bytes,
+                                       void* stream);
+
 /* ------------------------------------------------------------------------ */
 /* KV-cache movers (bit-exact)                                              */
 /* ------------------------------------------------------------------------ */

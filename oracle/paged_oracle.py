@@ -9,6 +9,7 @@ instead):
   decode_attention_loop   tests/kernels/test_attention.py:30-66  (ref_single_query_cached_kv_attention)
                           + :14-27 (ref_masked_attention)
   prefill_attention_loop  tests/kernels/test_attention.py:69-101 (ref_multi_query_kv_attention)
+  cached_prefill_attention_loop  tests/kernels/test_attention.py:104-156 (ref_multi_query_cached_kv_attention)
   reshape_and_cache       tests/kernels/test_cache.py:95-100
   gather_cached_kv        tests/kernels/test_cache.py:138-143
   copy_blocks             tests/kernels/test_cache.py:51-56
@@ -148,6 +149,62 @@ def prefill_attention_fp32(seq_lens: Sequence[int], query: torch.Tensor, key: to
         outs.append(torch.einsum("hqk,khd->qhd", torch.softmax(scores, dim=-1), v[start:end]))
         start = end
     return torch.cat(outs, dim=0) if outs else q[:0].clone()
+
+
+# ---------------------------------------------------------------------------
+# prompt chunks over the paged cache
+# ---------------------------------------------------------------------------
+def _context_rows(key_cache: torch.Tensor, value_cache: torch.Tensor, block_table: torch.Tensor, context_len: int):
+    """Keys / values of the first context_len cached tokens as [context_len, num_heads, head_size]
+    (the token-by-token gather of test_attention.py:131-143)."""
+    num_heads, head_size, block_size = value_cache.shape[1], value_cache.shape[2], value_cache.shape[3]
+    pos = torch.arange(context_len)
+    blocks = block_table.long()[pos // block_size]
+    offs = pos % block_size
+    keys = key_cache[blocks, :, :, offs, :].reshape(context_len, num_heads, head_size)
+    values = value_cache[blocks, :, :, offs]
+    return keys, values
+
+
+@torch.inference_mode()
+def cached_prefill_attention_loop(cu_query_lens: Sequence[int], query: torch.Tensor, key_cache: torch.Tensor,
+                                  value_cache: torch.Tensor, block_tables: torch.Tensor, context_lens,
+                                  scale: Optional[float] = None) -> torch.Tensor:
+    """Per sequence: gather the cached context, add a mask of -1e5 above the diagonal shifted by
+    context_len - query_len, dense attention with scores / softmax in the input dtype
+    (test_attention.py:104-156 with :14-27)."""
+    dtype = query.dtype
+    if scale is None:
+        scale = 1.0 / (query.shape[-1] ** 0.5)
+    outs = []
+    for i in range(len(cu_query_lens) - 1):
+        start, end = int(cu_query_lens[i]), int(cu_query_lens[i + 1])
+        qlen, ctx = end - start, int(context_lens[i])
+        keys, values = _context_rows(key_cache, value_cache, block_tables[i], ctx)
+        mask = (torch.triu(torch.ones(qlen, ctx), diagonal=ctx - qlen + 1) * -1e5).to(dtype)
+        scores = torch.einsum("qhd,khd->hqk", query[start:end] * scale, keys) + mask
+        probs = torch.softmax(scores, dim=-1)
+        outs.append(torch.einsum("hqk,khd->qhd", probs, values))
+    return torch.cat(outs, dim=0) if outs else query[:0].clone()
+
+
+@torch.inference_mode()
+def cached_prefill_attention_fp32(cu_query_lens: Sequence[int], query: torch.Tensor, key_cache: torch.Tensor,
+                                  value_cache: torch.Tensor, block_tables: torch.Tensor, context_lens,
+                                  scale: Optional[float] = None) -> torch.Tensor:
+    """The same with every intermediate in fp32 on the (already rounded) inputs and a true -inf mask."""
+    if scale is None:
+        scale = 1.0 / (query.shape[-1] ** 0.5)
+    outs = []
+    for i in range(len(cu_query_lens) - 1):
+        start, end = int(cu_query_lens[i]), int(cu_query_lens[i + 1])
+        qlen, ctx = end - start, int(context_lens[i])
+        keys, values = _context_rows(key_cache, value_cache, block_tables[i], ctx)
+        scores = torch.einsum("qhd,khd->hqk", query[start:end].float(), keys.float()) * scale
+        hidden = torch.triu(torch.ones(qlen, ctx, dtype=torch.bool), diagonal=ctx - qlen + 1)
+        scores = scores.masked_fill(hidden, float("-inf"))
+        outs.append(torch.einsum("hqk,khd->qhd", torch.softmax(scores, dim=-1), values.float()))
+    return torch.cat(outs, dim=0) if outs else query[:0].float().clone()
 
 
 # ---------------------------------------------------------------------------

@@ -141,6 +141,44 @@ def prefill_case(case_id: str) -> Dict[str, object]:
             "query": qkv[:, 0], "key": qkv[:, 1], "value": qkv[:, 2]}
 
 
+def cached_prefill_case_ids() -> List[str]:
+    ids = [f"{dt}-b16-d{d}-ref" for dt in DTYPES for d in HEAD_SIZES]
+    ids += [f"{dt}-b{b}-d{d}-unit" for dt in DTYPES for (b, d) in ((16, 128), (8, 80), (32, 96))]
+    return ids
+
+
+def cached_prefill_case(case_id: str) -> Dict[str, object]:
+    """Prompt chunks over the paged cache (ref_multi_query_cached_kv_attention, test_attention.py:104-156):
+    5 sequences, 3 heads, (query_len, context_len) = (1, 1) a lone first token, (70, 70) no cached prefix,
+    (130, 300) a chunk crossing a 128-row tile behind 170 cached tokens, (1, 257) a decode-like row,
+    (128, 133) a diagonal shifted by 5; block tables with repeated blocks and zero padding; the query
+    sliced out of a fused qkv tensor."""
+    dt, b, d, dist = case_id.split("-")
+    dtype, block_size, head_size = DTYPES[dt], int(b[1:]), int(d[1:])
+    seed = int(hashlib.sha256(("cached-prefill-" + case_id).encode()).hexdigest()[:8], 16)
+    rs = np.random.RandomState(seed)
+    num_heads, num_blocks = 3, 40
+    pairs = [(1, 1), (70, 70), (130, 300), (1, 257), (128, 133)]
+    qlens = [p[0] for p in pairs]
+    ctx = [p[1] for p in pairs]
+    cu = [0]
+    for n in qlens:
+        cu.append(cu[-1] + n)
+    x = 16 // torch.empty((), dtype=dtype).element_size()
+    qkv = _tensor(rs, (cu[-1], 3, num_heads, head_size), dtype, dist)
+    key_cache = _tensor(rs, (num_blocks, num_heads, head_size // x, block_size, x), dtype, dist)
+    value_cache = _tensor(rs, (num_blocks, num_heads, head_size, block_size), dtype, dist)
+    max_blocks = (max(ctx) + block_size - 1) // block_size + 1
+    tables = np.zeros((len(pairs), max_blocks), dtype=np.int32)
+    for i, c in enumerate(ctx):
+        n = (c + block_size - 1) // block_size
+        tables[i, :n] = rs.randint(0, num_blocks, size=n)
+    return {"dtype": dtype, "block_size": block_size, "head_size": head_size, "num_heads": num_heads,
+            "scale": float(1.0 / (head_size ** 0.5)), "qkv": qkv, "query": qkv[:, 0], "cu_query_lens": cu,
+            "key_cache": key_cache, "value_cache": value_cache, "block_tables": torch.from_numpy(tables),
+            "context_lens": torch.tensor(ctx, dtype=torch.int32)}
+
+
 def to_numpy(t: torch.Tensor) -> np.ndarray:
     """Bit pattern of a tensor as a numpy array (bf16/f16 -> uint16)."""
     t = t.contiguous()

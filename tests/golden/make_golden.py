@@ -12,6 +12,7 @@ source with `ast` and executed unmodified:
                                    ref_single_query_cached_kv_attention (:30-66)
                                    ref_multi_query_kv_attention (:69-101), with device='cuda' of its
                                    mask (:87) mapped to the CPU while it runs
+                                   ref_multi_query_cached_kv_attention (:104-156), likewise (:127)
   tests/kernels/test_cache.py      the reference loops inside run_copy_blocks (:51-56),
                                    run_reshape_and_cache (:95-100), run_gather_cached_kv (:138-143)
   tests/kernels/test_pos_encoding.py  rotate_half, apply_rotary_pos_emb, RefRotaryEmbeddingNeox (:12-77)
@@ -190,9 +191,39 @@ def make_prefill() -> None:
     json.dump(meta, open(os.path.join(HERE, "prefill_inputs.sha256.json"), "w"), indent=1, sort_keys=True)
 
 
+def make_cached_prefill() -> None:
+    """ref_multi_query_cached_kv_attention (tests/kernels/test_attention.py:104-156), unmodified; its
+    mask's device='cuda' (:127) is mapped to the CPU while it runs."""
+    ns = _functions(os.path.join(REF, "tests/kernels/test_attention.py"),
+                    {"ref_masked_attention", "ref_multi_query_cached_kv_attention"})
+    ref = ns["ref_multi_query_cached_kv_attention"]
+    real_to = torch.Tensor.to
+
+    def cpu_to(self, *args, **kwargs):
+        if kwargs.get("device") == "cuda":
+            kwargs["device"] = "cpu"
+        return real_to(self, *args, **kwargs)
+
+    out, meta = {}, {}
+    torch.Tensor.to = cpu_to
+    try:
+        for cid in cases.cached_prefill_case_ids():
+            c = cases.cached_prefill_case(cid)
+            with torch.inference_mode():
+                o = ref(c["cu_query_lens"], c["query"], c["key_cache"], c["value_cache"], c["block_tables"],
+                        c["context_lens"], c["dtype"])
+            out[cid] = cases.to_numpy(o)
+            meta[cid] = cases.digest(c["qkv"], c["key_cache"], c["value_cache"], c["block_tables"], c["context_lens"])
+            print(cid, float(o.float().abs().max()))
+    finally:
+        torch.Tensor.to = real_to
+    np.savez_compressed(os.path.join(HERE, "cached_prefill_golden.npz"), **out)
+    json.dump(meta, open(os.path.join(HERE, "cached_prefill_inputs.sha256.json"), "w"), indent=1, sort_keys=True)
+
+
 if __name__ == "__main__":
     torch.manual_seed(0)
-    which = sys.argv[1:] or ["attention", "cache", "rope", "prefill"]
+    which = sys.argv[1:] or ["attention", "cache", "rope", "prefill", "cached_prefill"]
     if "attention" in which:
         make_attention()
     if "cache" in which:
@@ -201,3 +232,5 @@ if __name__ == "__main__":
         make_rope()
     if "prefill" in which:
         make_prefill()
+    if "cached_prefill" in which:
+        make_cached_prefill()

@@ -1,0 +1,231 @@
+"""Prompt chunks over the paged cache (multi_query_cached_kv_attention): oracle pinned on the reference's
+ref_multi_query_cached_kv_attention (tests/kernels/test_attention.py:104-156, goldens made by
+tests/golden/make_golden.py), and the CUDA path (page gather + tcgen05 prompt kernel with a shifted
+diagonal) against the goldens and the oracle on the GPU."""
+import json
+import os
+import random
+
+import numpy as np
+import pytest
+import torch
+
+import cases
+import pa_testing as pt
+from oracle import paged_oracle
+
+GOLD = os.path.join(os.path.dirname(__file__), "golden")
+CP = np.load(os.path.join(GOLD, "cached_prefill_golden.npz"))
+CP_SHA = json.load(open(os.path.join(GOLD, "cached_prefill_inputs.sha256.json")))
+
+SAME_MATH_TOL = {torch.float16: 2e-3, torch.bfloat16: 1.6e-2, torch.float32: 1e-5}
+# north star: 1e-3 fp16, 1e-2 bf16; the fp32 path is exact fp32 arithmetic
+TOL = {torch.float16: 1e-3, torch.bfloat16: 1e-2, torch.float32: 1e-4}
+
+
+# ---------------------------------------------------------------------------- CPU: the oracle
+@pytest.mark.parametrize("cid", cases.cached_prefill_case_ids())
+def test_inputs_are_the_golden_inputs(cid):
+    c = cases.cached_prefill_case(cid)
+    assert cases.digest(c["qkv"], c["key_cache"], c["value_cache"], c["block_tables"], c["context_lens"]) == CP_SHA[cid]
+
+
+@pytest.mark.parametrize("cid", cases.cached_prefill_case_ids())
+def test_loop_oracle_matches_reference_output(cid):
+    c = cases.cached_prefill_case(cid)
+    gold = cases.from_numpy(CP[cid], c["dtype"]).float()
+    out = paged_oracle.cached_prefill_attention_loop(c["cu_query_lens"], c["query"], c["key_cache"], c["value_cache"],
+                                                     c["block_tables"], c["context_lens"]).float()
+    tol = SAME_MATH_TOL[c["dtype"]]
+    torch.testing.assert_close(out, gold, atol=tol * float(gold.abs().max()), rtol=tol)
+
+
+@pytest.mark.parametrize("cid", cases.cached_prefill_case_ids())
+def test_fp32_oracle_matches_reference_output(cid):
+    c = cases.cached_prefill_case(cid)
+    gold = cases.from_numpy(CP[cid], c["dtype"]).float()
+    truth = paged_oracle.cached_prefill_attention_fp32(c["cu_query_lens"], c["query"], c["key_cache"],
+                                                       c["value_cache"], c["block_tables"], c["context_lens"], c["scale"])
+    tol = SAME_MATH_TOL[c["dtype"]]
+    torch.testing.assert_close(truth, gold, atol=tol * float(gold.abs().max()), rtol=tol)
+
+
+def test_oracle_degenerates_to_its_neighbours():
+    """query_len == context_len is plain prompt attention; query_len == 1 is decode attention."""
+    c = cases.cached_prefill_case("f32-b16-d64-unit".replace("d64", "d128"))
+    kc, vc, bt = c["key_cache"], c["value_cache"], c["block_tables"]
+    ctx = [70, 33]
+    rows = [paged_oracle._context_rows(kc, vc, bt[i], n) for i, n in enumerate(ctx)]
+    keys = torch.cat([r[0] for r in rows]); values = torch.cat([r[1] for r in rows])
+    q = torch.randn((sum(ctx), 3, 128), generator=torch.Generator().manual_seed(0))
+    full = paged_oracle.cached_prefill_attention_fp32([0, 70, 103], q, kc, vc, bt[:2], ctx, c["scale"])
+    plain = paged_oracle.prefill_attention_fp32(ctx, q, keys, values, c["scale"])
+    torch.testing.assert_close(full, plain, atol=1e-6, rtol=1e-5)
+    one = paged_oracle.cached_prefill_attention_fp32([0, 1, 2], q[:2], kc, vc, bt[:2], ctx, c["scale"])
+    dec = paged_oracle.decode_attention_fp32(q[:2], kc, vc, bt[:2], torch.tensor(ctx, dtype=torch.int32), c["scale"])
+    torch.testing.assert_close(one, dec, atol=1e-6, rtol=1e-5)
+
+
+def test_symbols_exported():
+    from vllm_b200 import _cabi
+    lib = _cabi.lib()
+    assert hasattr(lib, "pa_multi_query_cached_kv_attention")
+    # K rows + V rows (256-byte aligned each) + one int32 slot per context token
+    assert lib.pa_multi_query_cached_kv_workspace_bytes(1000, 8, 128, _cabi.PA_F16) == 2 * 2048000 + 4000
+    assert lib.pa_multi_query_cached_kv_workspace_bytes(3, 1, 64, _cabi.PA_F32) == 2 * 768 + 12
+
+
+# ---------------------------------------------------------------------------- GPU
+def _run(c, dev="cuda", out_fill=float("nan")):
+    from vllm_b200 import attention_ops
+    qkv = c["qkv"].to(dev)
+    q = qkv[:, 0]
+    out = torch.full(q.shape, out_fill, dtype=c["dtype"], device=dev)
+    attention_ops.multi_query_cached_kv_attention(c["cu_query_lens"], out, q, c["key_cache"].to(dev),
+                                                  c["value_cache"].to(dev), c["scale"], c["block_tables"].to(dev),
+                                                  c["context_lens"], c["block_size"])
+    torch.cuda.synchronize()
+    return out.cpu()
+
+
+def _close(got, want, dtype, what=""):
+    tol = TOL[dtype]
+    got, want = got.float(), want.float()
+    assert torch.isfinite(got).all(), f"{what}: non-finite output"
+    err = (got - want).abs()
+    bound = tol * float(want.abs().max()) + tol * want.abs()
+    bad = err > bound
+    assert not bad.any(), f"{what}: {int(bad.sum())} elements off, max err {float(err.max()):.3e} vs max |want| {float(want.abs().max()):.3e}"
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("cid", cases.cached_prefill_case_ids())
+def test_matches_reference_golden(cid):
+    c = cases.cached_prefill_case(cid)
+    gold = cases.from_numpy(CP[cid], c["dtype"])
+    got = _run(c)
+    if cid.endswith("-ref"):
+        # the reference tests' own criterion (test_attention.py:224,265): atol 1e-3, rtol 1e-5 -- and ours
+        assert torch.allclose(got.float(), gold.float(), atol=1e-3, rtol=1e-5)
+    _close(got, gold, c["dtype"], cid)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("cid", cases.cached_prefill_case_ids())
+def test_matches_fp32_oracle(cid):
+    c = cases.cached_prefill_case(cid)
+    truth = paged_oracle.cached_prefill_attention_fp32(c["cu_query_lens"], c["query"], c["key_cache"],
+                                                       c["value_cache"], c["block_tables"], c["context_lens"], c["scale"])
+    _close(_run(c), truth, c["dtype"], cid)
+
+
+def _random_problem(dtype, d, b, pairs, h=4, seed=0, num_blocks=None):
+    rs = np.random.RandomState(seed)
+    ctx = [p[1] for p in pairs]
+    cu = [0]
+    for p in pairs:
+        cu.append(cu[-1] + p[0])
+    need = sum((c + b - 1) // b for c in ctx)
+    num_blocks = num_blocks or need + 3
+    x = 16 // torch.empty((), dtype=dtype).element_size()
+    qkv = cases._tensor(rs, (cu[-1], 3, h, d), dtype, "unit")
+    kc = cases._tensor(rs, (num_blocks, h, d // x, b, x), dtype, "unit")
+    vc = cases._tensor(rs, (num_blocks, h, d, b), dtype, "unit")
+    mb = max((c + b - 1) // b for c in ctx) + 2
+    tables = np.zeros((len(pairs), mb), dtype=np.int32)
+    perm = rs.permutation(num_blocks)
+    at = 0
+    for i, c in enumerate(ctx):
+        n = (c + b - 1) // b
+        tables[i, :n] = perm[at:at + n]
+        at += n
+    return {"dtype": dtype, "block_size": b, "head_size": d, "num_heads": h, "scale": d ** -0.5, "qkv": qkv,
+            "query": qkv[:, 0], "cu_query_lens": cu, "key_cache": kc, "value_cache": vc,
+            "block_tables": torch.from_numpy(tables), "context_lens": torch.tensor(ctx, dtype=torch.int32)}
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("dt", ["f16", "bf16", "f32"])
+@pytest.mark.parametrize("d,b", [(128, 16), (64, 8), (80, 32), (96, 16)])
+def test_chunked_prompts_of_many_shapes(dt, d, b):
+    """Chunks that start and end anywhere relative to the 128-token tiles and 256-row CTAs: the shifted
+    diagonal crosses one or two K/V tiles, tile B has as many tiles as tile A or one more."""
+    dtype = cases.DTYPES[dt]
+    rnd = random.Random(d * 31 + b + len(dt))
+    pairs = [(256, 256 + 128), (300, 300 + 1), (129, 129 + 127), (1, 700), (255, 511), (257, 1100), (7, 7)]
+    for _ in range(4):
+        q = rnd.randint(1, 600)
+        pairs.append((q, q + rnd.randint(0, 700)))
+    c = _random_problem(dtype, d, b, pairs, seed=d + b)
+    truth = paged_oracle.cached_prefill_attention_fp32(c["cu_query_lens"], c["query"], c["key_cache"], c["value_cache"],
+                                                       c["block_tables"], c["context_lens"], c["scale"])
+    _close(_run(c), truth, dtype, f"{dt} d{d} b{b} {pairs}")
+
+
+@pytest.mark.gpu
+def test_equals_plain_prompt_attention_and_decode():
+    """Size-independent properties: with no cached prefix the operator is the prompt kernel over the
+    gathered rows (bit-identical: same kernel, same tiles), and with one query row per sequence it
+    agrees with the decode kernel."""
+    from vllm_b200 import attention_ops, cache_ops
+    dtype = torch.bfloat16
+    pairs = [(513, 513), (64, 64), (1000, 1000)]
+    c = _random_problem(dtype, 128, 16, pairs, h=5, seed=9)
+    got = _run(c)
+    dev = "cuda"
+    kc, vc, bt = c["key_cache"].to(dev), c["value_cache"].to(dev), c["block_tables"]
+    slots = torch.cat([bt[i, torch.arange(n) // 16].int() * 16 + (torch.arange(n) % 16).int()
+                       for i, (n, _) in enumerate(pairs)]).int().to(dev)
+    n = slots.numel()
+    k = torch.empty((n, 5, 128), dtype=dtype, device=dev)
+    v = torch.empty_like(k)
+    cache_ops.gather_cached_kv(k, v, kc, vc, slots)
+    out = torch.empty_like(k)
+    attention_ops.multi_query_kv_attention(out, c["qkv"].to(dev)[:, 0], k, v, [p[0] for p in pairs], c["scale"])
+    torch.cuda.synchronize()
+    assert torch.equal(out.cpu().view(torch.int16), got.view(torch.int16))
+
+    ctx = [1, 16, 17, 300, 1025]
+    c = _random_problem(dtype, 128, 16, [(1, n) for n in ctx], h=5, seed=10)
+    got = _run(c)
+    dec = torch.empty((len(ctx), 5, 128), dtype=dtype, device=dev)
+    attention_ops.single_query_cached_kv_attention(dec, c["qkv"].to(dev)[:, 0], c["key_cache"].to(dev),
+                                                   c["value_cache"].to(dev), c["scale"], c["block_tables"].to(dev),
+                                                   c["context_lens"].to(dev), 16, max(ctx))
+    torch.cuda.synchronize()
+    _close(got, dec.cpu(), dtype, "one-row chunks vs decode kernel")
+
+
+@pytest.mark.gpu
+def test_untouched_rows_unwritten_slots_and_errors():
+    from vllm_b200 import attention_ops
+    dtype = torch.float16
+    pairs = [(5, 40), (200, 333)]
+    c = _random_problem(dtype, 128, 16, pairs, seed=3)
+    dev = "cuda"
+    # slots past each context (never written by the model) hold NaN: they must not reach the output
+    kc, vc = c["key_cache"].clone(), c["value_cache"].clone()
+    for i, (_, n) in enumerate(pairs):
+        last = int(c["block_tables"][i, (n - 1) // 16])
+        kc[last, :, :, n % 16 if n % 16 else 16:, :] = float("nan")
+        vc[last, :, :, n % 16 if n % 16 else 16:] = float("nan")
+    c["key_cache"], c["value_cache"] = kc, vc
+    n_valid, n_pad = c["cu_query_lens"][-1], 3
+    qkv = torch.cat([c["qkv"], torch.zeros((n_pad, 3, 4, 128), dtype=dtype)]).to(dev)
+    out = torch.full((n_valid + n_pad, 4, 128), 7.0, dtype=dtype, device=dev)
+    attention_ops.multi_query_cached_kv_attention(c["cu_query_lens"], out, qkv[:, 0], kc.to(dev), vc.to(dev), c["scale"],
+                                                  c["block_tables"].to(dev), c["context_lens"], 16)
+    torch.cuda.synchronize()
+    assert (out[n_valid:] == 7.0).all()
+    truth = paged_oracle.cached_prefill_attention_fp32(c["cu_query_lens"], c["query"], kc, vc, c["block_tables"],
+                                                       c["context_lens"], c["scale"])
+    _close(out[:n_valid].cpu(), truth, dtype)
+    with pytest.raises(RuntimeError):      # fewer cached tokens than query tokens
+        attention_ops.multi_query_cached_kv_attention([0, 5, 205], out, qkv[:, 0], kc.to(dev), vc.to(dev), c["scale"],
+                                                      c["block_tables"].to(dev), [4, 333], 16)
+    with pytest.raises(RuntimeError):      # context longer than the block table row
+        attention_ops.multi_query_cached_kv_attention([0, 5, 205], out, qkv[:, 0], kc.to(dev), vc.to(dev), c["scale"],
+                                                      c["block_tables"].to(dev), [40, 10 ** 6], 16)
+    # nothing to do
+    attention_ops.multi_query_cached_kv_attention([0], out, qkv[:, 0], kc.to(dev), vc.to(dev), c["scale"],
+                                                  c["block_tables"][:0].to(dev), [], 16)

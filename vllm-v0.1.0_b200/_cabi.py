@@ -70,6 +70,9 @@ SIGNATURES = {
                                        _f32, _i32, _vp]),
     "pa_prefill_attention_debug": (C.c_int, [_vp, _vp, _vp, _vp, C.POINTER(_i32), _i32, _i32, _i32, _i64, _i64, _i64,
                                              _i64, _f32, _i32, _vp, _vp]),
+    "pa_multi_query_cached_kv_workspace_bytes": (_i64, [_i64, _i32, _i32, _i32]),
+    "pa_multi_query_cached_kv_attention": (C.c_int, [_vp, _vp, _vp, _vp, _f32, _vp, C.POINTER(_i32), C.POINTER(_i32),
+                                                     _i32, _i32, _i32, _i32, _i32, _i64, _i64, _i32, _vp, _i64, _vp]),
     "pa_reshape_and_cache": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _i64, _i64, _i32, _vp]),
     "pa_gather_cached_kv": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _i64, _i64, _i32, _vp]),
     "pa_rotary_embedding_neox": (C.c_int, [_vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _i64, _i64, _i32, _vp]),

@@ -152,3 +152,83 @@ def multi_query_kv_attention(
                                                 value.stride(0), output.stride(0), float(scale), code,
                                                 debug.data_ptr(), stream)
     _cabi.check(rc)
+
+
+_workspaces = {}   # (device index, stream) -> uint8 tensor, grown on demand
+
+
+def _workspace(dev: torch.device, stream: int, nbytes: int) -> torch.Tensor:
+    key = (dev.index, stream)
+    ws = _workspaces.get(key)
+    if ws is None or ws.numel() < nbytes:
+        # the old buffer may still be in use by kernels queued on this stream; torch's caching allocator
+        # keeps a freed block stream-ordered, so dropping the reference is safe
+        ws = torch.empty(max(nbytes, 1 << 20) + 256, dtype=torch.uint8, device=dev)
+        _workspaces[key] = ws
+    return ws
+
+
+def multi_query_cached_kv_attention(
+    cu_query_lens,                # List[int] (or CPU tensor) [num_seqs + 1]: query tokens of sequence i are [cu[i], cu[i+1])
+    output: torch.Tensor,         # [num_tokens, num_heads, head_size]
+    query: torch.Tensor,          # [num_tokens, num_heads, head_size], row-strided
+    key_cache: torch.Tensor,      # [num_blocks, num_heads, head_size/x, block_size, x]
+    value_cache: torch.Tensor,    # [num_blocks, num_heads, head_size, block_size]
+    scale: float,
+    block_tables: torch.Tensor,   # [num_seqs, max_num_blocks_per_seq] int32, CUDA
+    context_lens,                 # [num_seqs]: List[int] or tensor (a CUDA tensor is read back: one sync)
+    block_size: int,
+) -> None:
+    """Prompt chunks over the paged cache: the new tokens of sequence i (whose K/V are already written
+    to the cache) attend to the context_lens[i] cached tokens, causally: row r sees cached tokens
+    0 .. r + (context_lens[i] - query_len_i).
+
+    Parity reference: ref_multi_query_cached_kv_attention (tests/kernels/test_attention.py:104-156), which
+    the reference tree keeps without a kernel; argument order follows single_query_cached_kv_attention
+    (csrc/attention.cpp:3-19) with the cumulative query lengths in front, as that reference takes them.
+    """
+    dev = query.device
+    for name, t in (("output", output), ("query", query), ("key_cache", key_cache), ("value_cache", value_cache),
+                    ("block_tables", block_tables)):
+        _require_cuda(name, t, dev)
+    code = _dtype_code(query)
+    if not (output.dtype == query.dtype == key_cache.dtype == value_cache.dtype):
+        raise RuntimeError("output, query, key_cache and value_cache must share one dtype")
+    if block_tables.dtype != torch.int32 or block_tables.dim() != 2 or not block_tables.is_contiguous():
+        raise RuntimeError("block_tables must be a contiguous int32 [num_seqs, max_num_blocks_per_seq] tensor")
+    if query.dim() != 3 or output.shape != query.shape or key_cache.dim() != 5 or value_cache.dim() != 4:
+        raise RuntimeError("unexpected tensor rank or shape")
+    num_tokens, num_heads, head_size = query.shape
+    for name, t in (("output", output), ("query", query)):
+        if t.stride(2) != 1 or t.stride(1) != head_size:
+            raise RuntimeError(f"{name} must be contiguous in its last two dimensions")
+    if not key_cache.is_contiguous() or not value_cache.is_contiguous():
+        raise RuntimeError("caches must be contiguous")
+    if value_cache.shape[1] != num_heads or value_cache.shape[2] != head_size or value_cache.shape[3] != block_size:
+        raise RuntimeError("value_cache shape does not match [num_blocks, num_heads, head_size, block_size]")
+    cu = [int(v) for v in (cu_query_lens.tolist() if isinstance(cu_query_lens, torch.Tensor) else cu_query_lens)]
+    ctx = [int(v) for v in (context_lens.tolist() if isinstance(context_lens, torch.Tensor) else context_lens)]
+    num_seqs = len(cu) - 1
+    if num_seqs < 0 or len(ctx) != num_seqs or block_tables.shape[0] != num_seqs:
+        raise RuntimeError("cu_query_lens, context_lens and block_tables disagree on the number of sequences")
+    if num_seqs == 0:
+        return
+    qlens = [cu[i + 1] - cu[i] for i in range(num_seqs)]
+    if cu[0] != 0 or min(qlens) < 0 or cu[-1] > num_tokens:
+        raise RuntimeError("cu_query_lens must start at 0, be non-decreasing and end within query")
+    lib = _cabi.lib()
+    need = lib.pa_multi_query_cached_kv_workspace_bytes(sum(ctx), num_heads, head_size, code)
+    if need < 0:
+        _cabi.check(int(need))
+    stream = torch.cuda.current_stream(dev).cuda_stream
+    ws = _workspace(dev, stream, int(need))
+    base = (ws.data_ptr() + 255) // 256 * 256
+    qarr = (C.c_int32 * num_seqs)(*qlens)
+    carr = (C.c_int32 * num_seqs)(*ctx)
+    with torch.cuda.device(dev):
+        rc = lib.pa_multi_query_cached_kv_attention(
+            output.data_ptr(), query.data_ptr(), key_cache.data_ptr(), value_cache.data_ptr(), float(scale),
+            block_tables.data_ptr(), qarr, carr, num_seqs, num_heads, head_size, int(block_size),
+            block_tables.shape[1], query.stride(0), output.stride(0), code, base,
+            ws.numel() - (base - ws.data_ptr()), stream)
+    _cabi.check(rc)

@@ -47,25 +47,27 @@ prefill_f32_kernel(const float* __restrict__ q, const float* __restrict__ k, con
   __shared__ float sk[KT][D];
   __shared__ float sv[KT][D];
   const int head = blockIdx.x;
-  const int tok0 = tiles.tok0[blockIdx.y], len = tiles.len[blockIdx.y], q0 = tiles.q0[blockIdx.y];
-  const int row = q0 + (threadIdx.x >> 1);          // query row inside the prompt
+  const int qtok0 = tiles.qtok0[blockIdx.y], qlen = tiles.qlen[blockIdx.y], q0 = tiles.q0[blockIdx.y];
+  const int ktok0 = tiles.ktok0[blockIdx.y], klen = tiles.klen[blockIdx.y];
+  const int koff = klen - qlen;                     // cached keys in front of the first query row
+  const int row = q0 + (threadIdx.x >> 1);          // query row inside the sequence
   const int half = threadIdx.x & 1;
-  const bool row_ok = row < len;
+  const bool row_ok = row < qlen;
   float qr[HD], acc[HD];
   {
-    const float* qp = q + (static_cast<int64_t>(tok0) + (row_ok ? row : q0)) * q_stride + head * D + half * HD;
+    const float* qp = q + (static_cast<int64_t>(qtok0) + (row_ok ? row : q0)) * q_stride + head * D + half * HD;
 #pragma unroll
     for (int i = 0; i < HD; ++i) { qr[i] = qp[i]; acc[i] = 0.f; }
   }
   float m = -CUDART_INF_F, l = 0.f;
-  const int kv_end = min(q0 + 64, len);
+  const int kv_end = min(q0 + 64 + koff, klen);
   for (int t0 = 0; t0 < kv_end; t0 += KT) {
     __syncthreads();
     for (int i = threadIdx.x; i < KT * D; i += blockDim.x) {
       const int t = i / D, d = i - t * D;
       const bool ok = t0 + t < kv_end;
-      sk[t][d] = ok ? k[(static_cast<int64_t>(tok0) + t0 + t) * k_stride + head * D + d] : 0.f;
-      sv[t][d] = ok ? v[(static_cast<int64_t>(tok0) + t0 + t) * v_stride + head * D + d] : 0.f;
+      sk[t][d] = ok ? k[(static_cast<int64_t>(ktok0) + t0 + t) * k_stride + head * D + d] : 0.f;
+      sv[t][d] = ok ? v[(static_cast<int64_t>(ktok0) + t0 + t) * v_stride + head * D + d] : 0.f;
     }
     __syncthreads();
     const int tmax = min(KT, kv_end - t0);
@@ -74,7 +76,7 @@ prefill_f32_kernel(const float* __restrict__ q, const float* __restrict__ k, con
 #pragma unroll
       for (int i = 0; i < HD; ++i) dot = fmaf(qr[i], sk[t][half * HD + i], dot);
       dot += __shfl_xor_sync(0xffffffffu, dot, 1);
-      if (t0 + t <= row) {                          // causal
+      if (t0 + t <= row + koff) {                   // causal
         const float sc = dot * scale_log2;
         const float mn = fmaxf(m, sc);
         const float alpha = ex2(m - mn), pr = ex2(sc - mn);
@@ -86,7 +88,7 @@ prefill_f32_kernel(const float* __restrict__ q, const float* __restrict__ k, con
     }
   }
   if (row_ok) {
-    float* op = out + (static_cast<int64_t>(tok0) + row) * out_stride + head * D + half * HD;
+    float* op = out + (static_cast<int64_t>(qtok0) + row) * out_stride + head * D + half * HD;
     const float inv = 1.f / l;
 #pragma unroll
     for (int i = 0; i < HD; ++i) op[i] = acc[i] * inv;
@@ -153,9 +155,12 @@ static int launch_f32(const void* q, const void* k, const void* v, void* out, in
   return check_cuda(cudaGetLastError(), "prefill_f32_kernel launch");
 }
 
+// key_lens == nullptr: plain prompt attention (every sequence's keys are its own query tokens' keys).
+// Otherwise sequence i has seq_lens[i] query rows behind key_lens[i] - seq_lens[i] earlier keys.
 static int prefill(void* out, const void* query, const void* key, const void* value, const int32_t* seq_lens,
-                   int32_t num_seqs, int32_t num_heads, int32_t head_size, int64_t q_stride, int64_t k_stride,
-                   int64_t v_stride, int64_t out_stride, float scale, int32_t dtype, float* dbg, cudaStream_t stream) {
+                   const int32_t* key_lens, int32_t num_seqs, int32_t num_heads, int32_t head_size, int64_t q_stride,
+                   int64_t k_stride, int64_t v_stride, int64_t out_stride, float scale, int32_t dtype, float* dbg,
+                   cudaStream_t stream) {
   if (dtype != PA_F16 && dtype != PA_BF16 && dtype != PA_F32)
     return set_error(PA_ERR_UNSUPPORTED_DTYPE, "unsupported data type: %d", dtype);
   if (head_size != 64 && head_size != 80 && head_size != 96 && head_size != 128)
@@ -169,27 +174,32 @@ static int prefill(void* out, const void* query, const void* key, const void* va
   if ((ptrs & 15u) || ((q_stride | k_stride | v_stride | out_stride) * es) % 16)
     return set_error(PA_ERR_INVALID_ARGUMENT, "query/key/value/out rows must be 16-byte aligned");
 
-  // tiles: one per 128 (16-bit) or 64 (fp32) query rows of a prompt; longest K/V span first
+  // tiles: one per 256 (16-bit) or 64 (fp32) query rows of a sequence; longest K/V span first
   const int rows = dtype == PA_F32 ? 64 : kPfRows;
-  struct Tile { int32_t tok0, len, q0; };
+  struct Tile { int32_t qtok0, qlen, q0, ktok0, klen, span; };
   std::vector<Tile> all;
-  int64_t tok = 0;
+  int64_t tok = 0, ktok = 0;
   for (int i = 0; i < num_seqs; ++i) {
     const int32_t len = seq_lens[i];
+    const int32_t klen = key_lens ? key_lens[i] : len;
     if (len < 0) return set_error(PA_ERR_INVALID_ARGUMENT, "negative prompt length");
-    if (tok + len > 0x7fffffff) return set_error(PA_ERR_INVALID_ARGUMENT, "too many tokens");
-    for (int32_t q0 = 0; q0 < len; q0 += rows) all.push_back({static_cast<int32_t>(tok), len, q0});
+    if (klen < len) return set_error(PA_ERR_INVALID_ARGUMENT, "sequence %d: %d keys for %d query tokens", i, klen, len);
+    if (tok + len > 0x7fffffff || ktok + klen > 0x7fffffff) return set_error(PA_ERR_INVALID_ARGUMENT, "too many tokens");
+    for (int32_t q0 = 0; q0 < len; q0 += rows)
+      all.push_back({static_cast<int32_t>(tok), len, q0, static_cast<int32_t>(ktok), klen,
+                     std::min(q0 + rows + (klen - len), klen)});
     tok += len;
+    ktok += klen;
   }
   if (all.empty()) return PA_OK;
-  std::stable_sort(all.begin(), all.end(), [](const Tile& a, const Tile& b) { return a.q0 > b.q0; });
+  std::stable_sort(all.begin(), all.end(), [](const Tile& a, const Tile& b) { return a.span > b.span; });
 
   CUtensorMap mq, mk, mv;
   const int dp = head_size <= 64 ? 64 : 128;
   if (dtype != PA_F32) {
     int rc = make_qkv_map(&mq, query, dtype, head_size, num_heads, tok, q_stride);
-    if (rc == PA_OK) rc = make_qkv_map(&mk, key, dtype, head_size, num_heads, tok, k_stride);
-    if (rc == PA_OK) rc = make_qkv_map(&mv, value, dtype, head_size, num_heads, tok, v_stride);
+    if (rc == PA_OK) rc = make_qkv_map(&mk, key, dtype, head_size, num_heads, ktok, k_stride);
+    if (rc == PA_OK) rc = make_qkv_map(&mv, value, dtype, head_size, num_heads, ktok, v_stride);
     if (rc != PA_OK) return rc;
   }
   PrefillParams p;
@@ -200,7 +210,8 @@ static int prefill(void* out, const void* query, const void* key, const void* va
   for (size_t begin = 0; begin < all.size(); begin += kPfMaxTiles) {
     const int n = static_cast<int>(std::min<size_t>(kPfMaxTiles, all.size() - begin));
     for (int i = 0; i < n; ++i) {
-      tiles.tok0[i] = all[begin + i].tok0; tiles.len[i] = all[begin + i].len; tiles.q0[i] = all[begin + i].q0;
+      const Tile& t = all[begin + i];
+      tiles.qtok0[i] = t.qtok0; tiles.qlen[i] = t.qlen; tiles.q0[i] = t.q0; tiles.ktok0[i] = t.ktok0; tiles.klen[i] = t.klen;
     }
     int rc;
     if (dtype == PA_F32) {
@@ -221,23 +232,135 @@ static int prefill(void* out, const void* query, const void* key, const void* va
   return PA_OK;
 }
 
+// ---------------------------------------------------------------------------
+// prompt chunks over the paged cache (multi_query_cached_kv_attention)
+//
+// Parity reference: ref_multi_query_cached_kv_attention (tests/kernels/test_attention.py:104-156): sequence i
+// has query_lens[i] new tokens whose keys / values are already in the cache together with the
+// context_lens[i] - query_lens[i] tokens before them; query row r sees keys 0 .. r + (context - query_len).
+// The reference tree keeps only that test reference (no kernel); here the pages of each context are gathered
+// once into packed [token][head][d] rows (the same tile mover as gather_cached_kv, slots generated on the
+// device from the block tables) and the tcgen05 prompt kernel runs over them with the diagonal shifted.
+// ---------------------------------------------------------------------------
+constexpr int kSlotSeqs = 1024;
+struct SlotSeqs {
+  int32_t ktok0[kSlotSeqs];  // first packed token of the sequence's context
+  int32_t klen[kSlotSeqs];   // context length
+};
+
+__global__ void __launch_bounds__(256)
+page_slots_kernel(const __grid_constant__ SlotSeqs t, const int32_t* __restrict__ block_tables, int32_t seq0,
+                  int32_t max_blocks, int32_t block_size, int32_t* __restrict__ slots) {
+  const int i = blockIdx.y;
+  const int klen = t.klen[i];
+  const int32_t* row = block_tables + static_cast<int64_t>(seq0 + i) * max_blocks;
+  for (int u = blockIdx.x * blockDim.x + threadIdx.x; u < klen; u += gridDim.x * blockDim.x)
+    slots[t.ktok0[i] + u] = row[u / block_size] * block_size + u % block_size;
+}
+
+static int64_t cached_ws_rows_bytes(int64_t tokens, int32_t num_heads, int32_t head_size, int32_t es) {
+  return (tokens * num_heads * head_size * es + 255) / 256 * 256;
+}
+
+static int cached_prefill(void* out, const void* query, const void* key_cache, const void* value_cache, float scale,
+                          const int32_t* block_tables, const int32_t* query_lens, const int32_t* context_lens,
+                          int32_t num_seqs, int32_t num_heads, int32_t head_size, int32_t block_size,
+                          int32_t max_blocks, int64_t q_stride, int64_t out_stride, int32_t dtype, void* workspace,
+                          int64_t workspace_bytes, cudaStream_t stream) {
+  if (dtype != PA_F16 && dtype != PA_BF16 && dtype != PA_F32)
+    return set_error(PA_ERR_UNSUPPORTED_DTYPE, "unsupported data type: %d", dtype);
+  if (head_size != 64 && head_size != 80 && head_size != 96 && head_size != 128)
+    return set_error(PA_ERR_UNSUPPORTED_HEAD_SIZE, "unsupported head size: %d", head_size);
+  if (block_size != 8 && block_size != 16 && block_size != 32)
+    return set_error(PA_ERR_UNSUPPORTED_BLOCK_SIZE, "unsupported block size: %d", block_size);
+  if (num_seqs < 0 || num_heads <= 0 || max_blocks < 0) return set_error(PA_ERR_INVALID_ARGUMENT, "bad sizes");
+  if (num_seqs == 0) return PA_OK;
+  if (!key_cache || !value_cache || !block_tables || !query_lens || !context_lens)
+    return set_error(PA_ERR_INVALID_ARGUMENT, "null pointer");
+  int64_t total = 0, max_ctx = 0, total_q = 0;
+  for (int i = 0; i < num_seqs; ++i) {
+    const int64_t c = context_lens[i], q = query_lens[i];
+    if (q < 0 || c < q) return set_error(PA_ERR_INVALID_ARGUMENT, "sequence %d: context %lld < query length %lld", i,
+                                         static_cast<long long>(c), static_cast<long long>(q));
+    if (c > static_cast<int64_t>(max_blocks) * block_size)
+      return set_error(PA_ERR_INVALID_ARGUMENT, "sequence %d: context %lld exceeds its block table (%d blocks of %d)", i,
+                       static_cast<long long>(c), max_blocks, block_size);
+    total += c; total_q += q; max_ctx = std::max(max_ctx, c);
+  }
+  if (total_q == 0) return PA_OK;
+  if (total > 0x7fffffff) return set_error(PA_ERR_INVALID_ARGUMENT, "too many context tokens");
+  const int es = dtype_size(dtype);
+  const int64_t rows_bytes = cached_ws_rows_bytes(total, num_heads, head_size, es);
+  const int64_t need = 2 * rows_bytes + total * 4;
+  if (!workspace || workspace_bytes < need || (reinterpret_cast<uintptr_t>(workspace) & 255u))
+    return set_error(PA_ERR_INVALID_ARGUMENT, "workspace of %lld bytes (256-byte aligned) needed, %lld given",
+                     static_cast<long long>(need), static_cast<long long>(workspace_bytes));
+  char* kws = static_cast<char*>(workspace);
+  char* vws = kws + rows_bytes;
+  int32_t* slots = reinterpret_cast<int32_t*>(vws + rows_bytes);
+
+  static thread_local SlotSeqs seqs;
+  int64_t ktok = 0;
+  for (int begin = 0; begin < num_seqs; begin += kSlotSeqs) {
+    const int n = std::min(kSlotSeqs, num_seqs - begin);
+    int32_t chunk_max = 1;
+    for (int i = 0; i < n; ++i) {
+      seqs.ktok0[i] = static_cast<int32_t>(ktok); seqs.klen[i] = context_lens[begin + i];
+      ktok += context_lens[begin + i];
+      chunk_max = std::max(chunk_max, context_lens[begin + i]);
+    }
+    page_slots_kernel<<<dim3((chunk_max + 255) / 256, n), 256, 0, stream>>>(seqs, block_tables, begin, max_blocks,
+                                                                           block_size, slots);
+    count_launch();
+    const int rc = check_cuda(cudaGetLastError(), "page_slots_kernel launch");
+    if (rc != PA_OK) return rc;
+  }
+  const int64_t row = static_cast<int64_t>(num_heads) * head_size;
+  int rc = pa_gather_cached_kv(kws, vws, key_cache, value_cache, slots, static_cast<int32_t>(total), num_heads,
+                               head_size, block_size, row, row, dtype, stream);
+  if (rc != PA_OK) return rc;
+  return prefill(out, query, kws, vws, query_lens, context_lens, num_seqs, num_heads, head_size, q_stride, row, row,
+                 out_stride, scale, dtype, nullptr, stream);
+}
+
 }  // namespace pa
 
 extern "C" {
 
+int64_t pa_multi_query_cached_kv_workspace_bytes(int64_t total_context_tokens, int32_t num_heads, int32_t head_size,
+                                                 int32_t dtype) {
+  if (total_context_tokens < 0 || num_heads <= 0 || head_size <= 0 ||
+      (dtype != PA_F16 && dtype != PA_BF16 && dtype != PA_F32))
+    return pa::set_error(PA_ERR_INVALID_ARGUMENT, "bad workspace query");
+  return 2 * pa::cached_ws_rows_bytes(total_context_tokens, num_heads, head_size, pa::dtype_size(dtype)) +
+         total_context_tokens * 4;
+}
+
+int pa_multi_query_cached_kv_attention(void* out, const void* query, const void* key_cache, const void* value_cache,
+                                       float scale, const int32_t* block_tables, const int32_t* query_lens,
+                                       const int32_t* context_lens, int32_t num_seqs, int32_t num_heads,
+                                       int32_t head_size, int32_t block_size, int32_t max_num_blocks_per_seq,
+                                       int64_t q_stride, int64_t out_stride, int32_t dtype, void* workspace,
+                                       int64_t workspace_bytes, void* stream) {
+  return pa::cached_prefill(out, query, key_cache, value_cache, scale, block_tables, query_lens, context_lens, num_seqs,
+                            num_heads, head_size, block_size, max_num_blocks_per_seq, q_stride, out_stride, dtype,
+                            workspace, workspace_bytes, static_cast<cudaStream_t>(stream));
+}
+
+
 int pa_prefill_attention(void* out, const void* query, const void* key, const void* value, const int32_t* seq_lens,
                          int32_t num_seqs, int32_t num_heads, int32_t head_size, int64_t q_stride, int64_t k_stride,
                          int64_t v_stride, int64_t out_stride, float scale, int32_t dtype, void* stream) {
-  return pa::prefill(out, query, key, value, seq_lens, num_seqs, num_heads, head_size, q_stride, k_stride, v_stride,
-                     out_stride, scale, dtype, nullptr, static_cast<cudaStream_t>(stream));
+  return pa::prefill(out, query, key, value, seq_lens, nullptr, num_seqs, num_heads, head_size, q_stride, k_stride,
+                     v_stride, out_stride, scale, dtype, nullptr, static_cast<cudaStream_t>(stream));
 }
 
 int pa_prefill_attention_debug(void* out, const void* query, const void* key, const void* value,
                                const int32_t* seq_lens, int32_t num_seqs, int32_t num_heads, int32_t head_size,
                                int64_t q_stride, int64_t k_stride, int64_t v_stride, int64_t out_stride, float scale,
                                int32_t dtype, float* debug, void* stream) {
-  return pa::prefill(out, query, key, value, seq_lens, num_seqs, num_heads, head_size, q_stride, k_stride, v_stride,
-                     out_stride, scale, dtype, debug, static_cast<cudaStream_t>(stream));
+  return pa::prefill(out, query, key, value, seq_lens, nullptr, num_seqs, num_heads, head_size, q_stride, k_stride,
+                     v_stride, out_stride, scale, dtype, debug, static_cast<cudaStream_t>(stream));
 }
 
 }  // extern "C"

@@ -25,10 +25,15 @@ constexpr int kPfCols = 128;       // K/V tokens per tile
 constexpr int kPfMaxTiles = 1024;  // CTAs per launch (the table travels as a kernel parameter)
 constexpr int kPfThreads = 384;   // 8 softmax warps + producer + issuer + 2 idle warps that only donate registers
 
+// A sequence has qlen query rows (packed from token qtok0 of q / out) and klen >= qlen keys (packed from
+// token ktok0 of k / v).  Query row i sees keys 0 .. i + (klen - qlen): plain prompt attention is
+// klen == qlen; klen > qlen is a prompt chunk behind klen - qlen tokens that are already cached.
 struct PrefillTiles {
-  int32_t tok0[kPfMaxTiles];  // first token of the prompt in the packed batch
-  int32_t len[kPfMaxTiles];   // prompt length
-  int32_t q0[kPfMaxTiles];    // first query row of this CTA inside the prompt (multiple of its row count)
+  int32_t qtok0[kPfMaxTiles];  // first query token of the sequence in the packed batch
+  int32_t qlen[kPfMaxTiles];   // query rows of the sequence
+  int32_t q0[kPfMaxTiles];     // first query row of this CTA inside the sequence (multiple of its row count)
+  int32_t ktok0[kPfMaxTiles];  // first key token of the sequence in the packed keys / values
+  int32_t klen[kPfMaxTiles];   // keys of the sequence
 };
 
 struct PrefillParams {
@@ -106,10 +111,13 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int head = blockIdx.x;
-  const int tok0 = tiles.tok0[blockIdx.y], len = tiles.len[blockIdx.y], q0 = tiles.q0[blockIdx.y];
-  // K/V tiles each query tile visits: everything up to and including its diagonal tile
-  const int nA = q0 / kPfCols + 1;
-  const int nB = (q0 + 128 < len) ? nA + 1 : 0;
+  const int qtok0 = tiles.qtok0[blockIdx.y], qlen = tiles.qlen[blockIdx.y], q0 = tiles.q0[blockIdx.y];
+  const int ktok0 = tiles.ktok0[blockIdx.y], klen = tiles.klen[blockIdx.y];
+  const int koff = klen - qlen;                   // keys in front of the first query row
+  // K/V tiles each query tile visits: everything up to and including the tile that holds the last key its
+  // last row sees (plain prompts: its diagonal tile).  nB is nA or nA + 1.
+  const int nA = min(q0 + 127 + koff, klen - 1) / kPfCols + 1;
+  const int nB = (q0 + 128 < qlen) ? min(q0 + 255 + koff, klen - 1) / kPfCols + 1 : 0;
   const int nmax = nB > nA ? nB : nA;
 
   if (tid == 0) {
@@ -139,17 +147,17 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant
         for (int a = 0; a < kAtoms; ++a) tc05::tma_load_3d(dst + a * kAtomBytes, map, a * 64, head, row0, bar);
       };
       mbar_expect_tx(bar_q, (nB ? 2 : 1) * kTileBytes);
-      load_tile(&tmq, sQ, tok0 + q0, bar_q);
-      if (nB) load_tile(&tmq, sQ + kTileBytes, tok0 + q0 + 128, bar_q);
+      load_tile(&tmq, sQ, qtok0 + q0, bar_q);
+      if (nB) load_tile(&tmq, sQ + kTileBytes, qtok0 + q0 + 128, bar_q);
       for (int j = 0; j < nmax; ++j) {
         const int s = j & 1;
         const uint32_t ph = ((j >> 1) & 1) ^ 1;    // first use of a stage passes immediately
         mbar_wait(bar_ke + 8 * s, ph);
         mbar_expect_tx(bar_kf + 8 * s, kTileBytes);
-        load_tile(&tmk, sK + s * kTileBytes, tok0 + j * kPfCols, bar_kf + 8 * s);
+        load_tile(&tmk, sK + s * kTileBytes, ktok0 + j * kPfCols, bar_kf + 8 * s);
         mbar_wait(bar_ve + 8 * s, ph);
         mbar_expect_tx(bar_vf + 8 * s, kTileBytes);
-        load_tile(&tmv, sV + s * kTileBytes, tok0 + j * kPfCols, bar_vf + 8 * s);
+        load_tile(&tmv, sV + s * kTileBytes, ktok0 + j * kPfCols, bar_vf + 8 * s);
       }
     }
   } else if (warp == 9) {
@@ -238,8 +246,11 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant
 #pragma unroll
           for (int i = 0; i < 32; ++i) p.dbg[r * 128 + c * 32 + i] = __uint_as_float(s[c][i]);
       }
-      if (j == ni - 1) {                            // the diagonal tile is the only one that needs masking
-        const int lim = min(r, len - 1 - qi0);      // last valid column of this row
+      // only tiles reaching past the last key of the tile's FIRST row need masking: the diagonal tile of a
+      // plain prompt, at most the last two tiles when cached keys shift the diagonal off the tile grid.
+      // A row wholly masked in such a tile (never tile 0) keeps its running maximum: all its p are 0.
+      if ((j + 1) * kPfCols - 1 > min(qi0 + koff, klen - 1)) {
+        const int lim = min(qi0 + r + koff, klen - 1) - j * kPfCols;   // last valid column of this row
 #pragma unroll
         for (int c = 0; c < 4; ++c)
 #pragma unroll
@@ -312,10 +323,10 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant
       mbar_wait(bar_o + 8 * grp, 0);
       tc05::fence_after_sync();
       const int D = p.head_size;
-      const bool row_ok = qi0 + r < len;
+      const bool row_ok = qi0 + r < qlen;
       const float inv = 1.f / l_run;
       char* orow = reinterpret_cast<char*>(p.out) +
-                   ((static_cast<int64_t>(tok0) + qi0 + r) * p.out_stride + static_cast<int64_t>(head) * D) * 2;
+                   ((static_cast<int64_t>(qtok0) + qi0 + r) * p.out_stride + static_cast<int64_t>(head) * D) * 2;
 #pragma unroll
       for (int c = 0; c < DP / 32; ++c) {
         uint32_t o[32];
