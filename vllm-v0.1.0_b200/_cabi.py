@@ -10,8 +10,7 @@ import os
 import threading
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-# PA_LIBRARY: a differently tuned build of the same library (tools/prefill_variants.py), never a fallback
-LIB_PATH = os.environ.get("PA_LIBRARY") or os.path.join(_HERE, "lib", "libpaged_b200.so")
+LIB_PATH = os.path.join(_HERE, "lib", "libpaged_b200.so")
 
 PA_F16, PA_BF16, PA_F32 = 0, 1, 2
 PA_COPY_D2D, PA_COPY_D2H, PA_COPY_H2D = 0, 1, 2

@@ -23,10 +23,6 @@ namespace pa {
 constexpr int kPfRows = 256;       // query rows per CTA (two tiles of 128 = TMEM lanes)
 constexpr int kPfCols = 128;       // K/V tokens per tile
 constexpr int kPfMaxTiles = 1024;  // CTAs per launch (the table travels as a kernel parameter)
-#ifndef PA_PREFILL_POLY_MASK
-#define PA_PREFILL_POLY_MASK 0x00   // bit k: pair k of every 8 takes ex2_poly2.  Measured on B200 (8x4096 bf16): 0x00 916, 0x10 912, 0x12 894, 0x52 862, 0xff 766 TFLOP/s -- the section is issue-bound, not MUFU-bound, so the default is off
-#endif
-constexpr unsigned kPfPolyMask = PA_PREFILL_POLY_MASK;
 constexpr int kPfThreads = 384;   // 8 softmax warps + producer + issuer + 2 idle warps that only donate registers
 
 // A sequence has qlen query rows (packed from token qtok0 of q / out) and klen >= qlen keys (packed from
@@ -78,40 +74,6 @@ __device__ __forceinline__ void fadd2(float& a0, float& a1, float b0, float b1) 
   asm("{.reg .b64 ra, rb;\n\tmov.b64 ra, {%0, %1};\n\tmov.b64 rb, {%2, %3};\n\tadd.rn.f32x2 ra, ra, rb;\n\t"
       "mov.b64 {%0, %1}, ra;}"
       : "+f"(a0), "+f"(a1) : "f"(b0), "f"(b1));
-}
-
-// 2^x for two values on the FMA pipe instead of the special-function unit (which is the scarce unit of the
-// exponential section: 16 results per clock per SM against 128 fp32 lanes).  Cody-Waite: j = rint(x) through the
-// 1.5 * 2^23 magic constant, f = x - j in [-0.5, 0.5], 2^f by a degree-3 minimax polynomial (relative error
-// 7.5e-5, below the half-ulp of the 16-bit probabilities it feeds), then j is added into the exponent field.
-// x is clamped at -125 (2^-125: masked -inf logits become ~2e-38 instead of 0, far below anything a sum keeps).
-// volatile: stays inside the ping-pong section like ex2_pinned.
-__device__ __forceinline__ void ex2_poly2(float& p0, float& p1, float x0, float x1) {
-  x0 = fmaxf(x0, -125.f); x1 = fmaxf(x1, -125.f);
-  uint32_t r0, r1;
-  asm volatile(
-      "{.reg .b64 x, t, j, f, p, m, c;\n\t"
-      ".reg .b32 tl, th, pl, ph;\n\t"
-      "mov.b64 x, {%2, %3};\n\t"
-      "mov.b64 m, {0f4B400000, 0f4B400000};\n\t"
-      "add.rn.f32x2 t, x, m;\n\t"
-      "sub.rn.f32x2 j, t, m;\n\t"
-      "sub.rn.f32x2 f, x, j;\n\t"
-      "mov.b64 p, {0f3D61FBB0, 0f3D61FBB0};\n\t"
-      "mov.b64 c, {0f3E786F0D, 0f3E786F0D};\n\t"
-      "fma.rn.f32x2 p, p, f, c;\n\t"
-      "mov.b64 c, {0f3F31798D, 0f3F31798D};\n\t"
-      "fma.rn.f32x2 p, p, f, c;\n\t"
-      "mov.b64 c, {0f3F7FFB49, 0f3F7FFB49};\n\t"
-      "fma.rn.f32x2 p, p, f, c;\n\t"
-      "mov.b64 {tl, th}, t;\n\t"
-      "mov.b64 {pl, ph}, p;\n\t"
-      "shl.b32 tl, tl, 23;\n\t"
-      "shl.b32 th, th, 23;\n\t"
-      "add.s32 %0, pl, tl;\n\t"
-      "add.s32 %1, ph, th;}"
-      : "=r"(r0), "=r"(r1) : "f"(x0), "f"(x1));
-  p0 = __uint_as_float(r0); p1 = __uint_as_float(r1);
 }
 
 // Named barriers 1 and 2 hand the special-function unit back and forth between the two softmax groups
@@ -341,12 +303,7 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant
           for (int i = 0; i < 32; i += 2) {
             float a0, a1;
             ffma2(a0, a1, __uint_as_float(s[c2 * 2 + h][i]), __uint_as_float(s[c2 * 2 + h][i + 1]), sc, neg_m);
-            float p0, p1;
-            if ((kPfPolyMask >> ((i >> 1) & 7)) & 1) {     // compile-time choice (the loop is fully unrolled)
-              ex2_poly2(p0, p1, a0, a1);
-            } else {
-              p0 = ex2_pinned(a0); p1 = ex2_pinned(a1);
-            }
+            const float p0 = ex2_pinned(a0), p1 = ex2_pinned(a1);
             fadd2(sum[(i >> 1) & 1 ? 2 : 0], sum[(i >> 1) & 1 ? 3 : 1], p0, p1);
             pk[h * 16 + (i >> 1)] = pack2<T>(p0, p1);
           }
