@@ -227,10 +227,14 @@ PA_API int pa_prefill_attention_debug(void* out, const void* query, const void* 
  * (DEVICE, int32 [num_seqs][max_num_blocks_per_seq]) as for pa_decode_attention.
  * query_lens and context_lens are HOST arrays (the reference keeps cu_query_lens as a
  * Python list).  head_size in {64, 80, 96, 128}, block_size in {8, 16, 32}.
- * workspace: DEVICE scratch, 256-byte aligned, at least
- * pa_multi_query_cached_kv_workspace_bytes(sum(context_lens), ...) bytes, owned by the
- * caller and free for reuse once the stream has passed this call.
- * Launches: slot generation, one page gather, the prompt-attention kernel.
+ * PA_F16 / PA_BF16: ONE launch -- the tcgen05 prompt kernel's producer warps copy the pages
+ * themselves (cp.async, 16-byte chunks placed where the 128-byte swizzle of the operand tile
+ * wants them; tokens past the context zero-filled); no scratch: workspace may be NULL,
+ * pa_multi_query_cached_kv_workspace_bytes returns 0.
+ * PA_F32 (a test-matrix case): slot generation + page gather into `workspace` (DEVICE scratch,
+ * 256-byte aligned, at least pa_multi_query_cached_kv_workspace_bytes(sum(context_lens), ...)
+ * bytes, owned by the caller, free for reuse once the stream has passed this call) + the exact
+ * fp32 SIMT prompt kernel.
  */
 PA_API int64_t pa_multi_query_cached_kv_workspace_bytes(int64_t total_context_tokens,
                                                  int32_t num_heads, int32_t head_size,

@@ -70,8 +70,10 @@ def test_symbols_exported():
     from vllm_b200 import _cabi
     lib = _cabi.lib()
     assert hasattr(lib, "pa_multi_query_cached_kv_attention")
-    # K rows + V rows (256-byte aligned each) + one int32 slot per context token
-    assert lib.pa_multi_query_cached_kv_workspace_bytes(1000, 8, 128, _cabi.PA_F16) == 2 * 2048000 + 4000
+    # 16-bit types read the pages directly; fp32 gathers: K rows + V rows (256-byte aligned each) + one int32 slot
+    # per context token
+    assert lib.pa_multi_query_cached_kv_workspace_bytes(1000, 8, 128, _cabi.PA_F16) == 0
+    assert lib.pa_multi_query_cached_kv_workspace_bytes(1000, 8, 128, _cabi.PA_F32) == 2 * 4096000 + 4000
     assert lib.pa_multi_query_cached_kv_workspace_bytes(3, 1, 64, _cabi.PA_F32) == 2 * 768 + 12
 
 
@@ -164,9 +166,8 @@ def test_chunked_prompts_of_many_shapes(dt, d, b):
 
 @pytest.mark.gpu
 def test_equals_plain_prompt_attention_and_decode():
-    """Size-independent properties: with no cached prefix the operator is the prompt kernel over the
-    gathered rows (bit-identical: same kernel, same tiles), and with one query row per sequence it
-    agrees with the decode kernel."""
+    """Size-independent properties: with no cached prefix the operator agrees with the prompt kernel over
+    the gathered rows, and with one query row per sequence with the decode kernel."""
     from vllm_b200 import attention_ops, cache_ops
     dtype = torch.bfloat16
     pairs = [(513, 513), (64, 64), (1000, 1000)]
@@ -183,7 +184,7 @@ def test_equals_plain_prompt_attention_and_decode():
     out = torch.empty_like(k)
     attention_ops.multi_query_kv_attention(out, c["qkv"].to(dev)[:, 0], k, v, [p[0] for p in pairs], c["scale"])
     torch.cuda.synchronize()
-    assert torch.equal(out.cpu().view(torch.int16), got.view(torch.int16))
+    _close(got, out.cpu(), dtype, "no cached prefix vs the prompt kernel over gathered rows")
 
     ctx = [1, 16, 17, 300, 1025]
     c = _random_problem(dtype, 128, 16, [(1, n) for n in ctx], h=5, seed=10)

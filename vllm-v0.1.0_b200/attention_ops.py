@@ -221,14 +221,17 @@ def multi_query_cached_kv_attention(
     if need < 0:
         _cabi.check(int(need))
     stream = torch.cuda.current_stream(dev).cuda_stream
-    ws = _workspace(dev, stream, int(need))
-    base = (ws.data_ptr() + 255) // 256 * 256
+    if need:
+        ws = _workspace(dev, stream, int(need))
+        base = (ws.data_ptr() + 255) // 256 * 256
+        ws_bytes = ws.numel() - (base - ws.data_ptr())
+    else:                                           # 16-bit types: the kernel reads the pages itself
+        base, ws_bytes = None, 0
     qarr = (C.c_int32 * num_seqs)(*qlens)
     carr = (C.c_int32 * num_seqs)(*ctx)
     with torch.cuda.device(dev):
         rc = lib.pa_multi_query_cached_kv_attention(
             output.data_ptr(), query.data_ptr(), key_cache.data_ptr(), value_cache.data_ptr(), float(scale),
             block_tables.data_ptr(), qarr, carr, num_seqs, num_heads, head_size, int(block_size),
-            block_tables.shape[1], query.stride(0), output.stride(0), code, base,
-            ws.numel() - (base - ws.data_ptr()), stream)
+            block_tables.shape[1], query.stride(0), output.stride(0), code, base, ws_bytes, stream)
     _cabi.check(rc)

@@ -133,16 +133,25 @@ static int make_qkv_map(CUtensorMap* map, const void* base, int dtype, int head_
   return PA_OK;
 }
 
-template <typename T, int DP>
+template <typename T, int DP, bool kPaged>
 static int launch_tc(const CUtensorMap& mq, const CUtensorMap& mk, const CUtensorMap& mv, const PrefillTiles& tiles,
                      int ntiles, const PrefillParams& p, cudaStream_t stream) {
   constexpr int smem = 6 * (DP / 64) * 128 * 128 + 1024 + 128;
-  auto kern = prefill_tc_kernel<T, DP>;
+  auto kern = prefill_tc_kernel<T, DP, kPaged>;
   PA_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
   kern<<<dim3(p.num_heads, ntiles), kPfThreads, smem, stream>>>(mq, mk, mv, tiles, p);
   count_launch();
   return check_cuda(cudaGetLastError(), "prefill_tc_kernel launch");
 }
+
+// keys / values in the paged caches instead of packed rows (16-bit types)
+struct PagedKV {
+  const void* key_cache;
+  const void* value_cache;
+  const int32_t* block_tables;
+  int32_t max_blocks;
+  int32_t block_size;
+};
 
 template <int D>
 static int launch_f32(const void* q, const void* k, const void* v, void* out, int64_t qs, int64_t ks, int64_t vs,
@@ -160,13 +169,14 @@ static int launch_f32(const void* q, const void* k, const void* v, void* out, in
 static int prefill(void* out, const void* query, const void* key, const void* value, const int32_t* seq_lens,
                    const int32_t* key_lens, int32_t num_seqs, int32_t num_heads, int32_t head_size, int64_t q_stride,
                    int64_t k_stride, int64_t v_stride, int64_t out_stride, float scale, int32_t dtype, float* dbg,
-                   cudaStream_t stream) {
+                   cudaStream_t stream, const PagedKV* paged = nullptr) {
   if (dtype != PA_F16 && dtype != PA_BF16 && dtype != PA_F32)
     return set_error(PA_ERR_UNSUPPORTED_DTYPE, "unsupported data type: %d", dtype);
   if (head_size != 64 && head_size != 80 && head_size != 96 && head_size != 128)
     return set_error(PA_ERR_UNSUPPORTED_HEAD_SIZE, "unsupported head size: %d", head_size);
   if (num_seqs < 0 || num_heads <= 0 || num_heads > 65535) return set_error(PA_ERR_INVALID_ARGUMENT, "bad sizes");
   if (num_seqs == 0) return PA_OK;
+  if (paged) { key = paged->key_cache; value = paged->value_cache; k_stride = v_stride = 8; }
   if (!out || !query || !key || !value || !seq_lens) return set_error(PA_ERR_INVALID_ARGUMENT, "null pointer");
   const int es = dtype_size(dtype);
   const uintptr_t ptrs = reinterpret_cast<uintptr_t>(out) | reinterpret_cast<uintptr_t>(query) |
@@ -186,7 +196,7 @@ static int prefill(void* out, const void* query, const void* key, const void* va
     if (klen < len) return set_error(PA_ERR_INVALID_ARGUMENT, "sequence %d: %d keys for %d query tokens", i, klen, len);
     if (tok + len > 0x7fffffff || ktok + klen > 0x7fffffff) return set_error(PA_ERR_INVALID_ARGUMENT, "too many tokens");
     for (int32_t q0 = 0; q0 < len; q0 += rows)
-      all.push_back({static_cast<int32_t>(tok), len, q0, static_cast<int32_t>(ktok), klen,
+      all.push_back({static_cast<int32_t>(tok), len, q0, paged ? i : static_cast<int32_t>(ktok), klen,
                      std::min(q0 + rows + (klen - len), klen)});
     tok += len;
     ktok += klen;
@@ -198,13 +208,20 @@ static int prefill(void* out, const void* query, const void* key, const void* va
   const int dp = head_size <= 64 ? 64 : 128;
   if (dtype != PA_F32) {
     int rc = make_qkv_map(&mq, query, dtype, head_size, num_heads, tok, q_stride);
-    if (rc == PA_OK) rc = make_qkv_map(&mk, key, dtype, head_size, num_heads, ktok, k_stride);
-    if (rc == PA_OK) rc = make_qkv_map(&mv, value, dtype, head_size, num_heads, ktok, v_stride);
+    if (paged) { mk = mq; mv = mq; }               // unused by the paged kernel
+    if (rc == PA_OK && !paged) rc = make_qkv_map(&mk, key, dtype, head_size, num_heads, ktok, k_stride);
+    if (rc == PA_OK && !paged) rc = make_qkv_map(&mv, value, dtype, head_size, num_heads, ktok, v_stride);
     if (rc != PA_OK) return rc;
   }
   PrefillParams p;
   p.out = out; p.out_stride = out_stride; p.num_heads = num_heads; p.head_size = head_size;
   p.scale_log2 = scale * 1.4426950408889634f; p.dbg = dbg;
+  p.key_cache = nullptr; p.value_cache = nullptr; p.block_tables = nullptr; p.max_blocks = 0; p.block_shift = 0;
+  if (paged) {
+    p.key_cache = paged->key_cache; p.value_cache = paged->value_cache; p.block_tables = paged->block_tables;
+    p.max_blocks = paged->max_blocks;
+    while ((1 << p.block_shift) < paged->block_size) ++p.block_shift;
+  }
 
   static thread_local PrefillTiles tiles;
   for (size_t begin = 0; begin < all.size(); begin += kPfMaxTiles) {
@@ -221,10 +238,13 @@ static int prefill(void* out, const void* query, const void* key, const void* va
         case 96:  rc = launch_f32<96>(query, key, value, out, q_stride, k_stride, v_stride, out_stride, tiles, n, num_heads, p.scale_log2, stream); break;
         default:  rc = launch_f32<128>(query, key, value, out, q_stride, k_stride, v_stride, out_stride, tiles, n, num_heads, p.scale_log2, stream); break;
       }
+    } else if (paged) {
+      if (dtype == PA_F16) rc = dp == 64 ? launch_tc<F16, 64, true>(mq, mk, mv, tiles, n, p, stream) : launch_tc<F16, 128, true>(mq, mk, mv, tiles, n, p, stream);
+      else rc = dp == 64 ? launch_tc<BF16, 64, true>(mq, mk, mv, tiles, n, p, stream) : launch_tc<BF16, 128, true>(mq, mk, mv, tiles, n, p, stream);
     } else if (dtype == PA_F16) {
-      rc = dp == 64 ? launch_tc<F16, 64>(mq, mk, mv, tiles, n, p, stream) : launch_tc<F16, 128>(mq, mk, mv, tiles, n, p, stream);
+      rc = dp == 64 ? launch_tc<F16, 64, false>(mq, mk, mv, tiles, n, p, stream) : launch_tc<F16, 128, false>(mq, mk, mv, tiles, n, p, stream);
     } else {
-      rc = dp == 64 ? launch_tc<BF16, 64>(mq, mk, mv, tiles, n, p, stream) : launch_tc<BF16, 128>(mq, mk, mv, tiles, n, p, stream);
+      rc = dp == 64 ? launch_tc<BF16, 64, false>(mq, mk, mv, tiles, n, p, stream) : launch_tc<BF16, 128, false>(mq, mk, mv, tiles, n, p, stream);
     }
     if (rc != PA_OK) return rc;
     p.dbg = nullptr;
@@ -238,9 +258,10 @@ static int prefill(void* out, const void* query, const void* key, const void* va
 // Parity reference: ref_multi_query_cached_kv_attention (tests/kernels/test_attention.py:104-156): sequence i
 // has query_lens[i] new tokens whose keys / values are already in the cache together with the
 // context_lens[i] - query_lens[i] tokens before them; query row r sees keys 0 .. r + (context - query_len).
-// The reference tree keeps only that test reference (no kernel); here the pages of each context are gathered
-// once into packed [token][head][d] rows (the same tile mover as gather_cached_kv, slots generated on the
-// device from the block tables) and the tcgen05 prompt kernel runs over them with the diagonal shifted.
+// The reference tree keeps only that test reference (no kernel).  16-bit types: the tcgen05 prompt kernel with
+// the diagonal shifted by context - query_len and a page producer (prefill_tc.cuh, kPaged) -- one launch, no
+// scratch.  fp32: the pages of each context are gathered once into packed [token][head][d] rows (the tile mover
+// of gather_cached_kv, slots generated on the device from the block tables) for the exact SIMT kernel.
 // ---------------------------------------------------------------------------
 constexpr int kSlotSeqs = 1024;
 struct SlotSeqs {
@@ -289,6 +310,14 @@ static int cached_prefill(void* out, const void* query, const void* key_cache, c
   }
   if (total_q == 0) return PA_OK;
   if (total > 0x7fffffff) return set_error(PA_ERR_INVALID_ARGUMENT, "too many context tokens");
+  if (dtype != PA_F32) {
+    // 16-bit: one launch; the prompt kernel's producer warps read the pages themselves (no gather, no scratch)
+    if ((reinterpret_cast<uintptr_t>(key_cache) | reinterpret_cast<uintptr_t>(value_cache)) & 15u)
+      return set_error(PA_ERR_INVALID_ARGUMENT, "caches must be 16-byte aligned");
+    const PagedKV paged = {key_cache, value_cache, block_tables, max_blocks, block_size};
+    return prefill(out, query, nullptr, nullptr, query_lens, context_lens, num_seqs, num_heads, head_size, q_stride, 0, 0,
+                   out_stride, scale, dtype, nullptr, stream, &paged);
+  }
   const int es = dtype_size(dtype);
   const int64_t rows_bytes = cached_ws_rows_bytes(total, num_heads, head_size, es);
   const int64_t need = 2 * rows_bytes + total * 4;
@@ -332,6 +361,7 @@ int64_t pa_multi_query_cached_kv_workspace_bytes(int64_t total_context_tokens, i
   if (total_context_tokens < 0 || num_heads <= 0 || head_size <= 0 ||
       (dtype != PA_F16 && dtype != PA_BF16 && dtype != PA_F32))
     return pa::set_error(PA_ERR_INVALID_ARGUMENT, "bad workspace query");
+  if (dtype != PA_F32) return 0;                   // 16-bit types read the pages directly
   return 2 * pa::cached_ws_rows_bytes(total_context_tokens, num_heads, head_size, pa::dtype_size(dtype)) +
          total_context_tokens * 4;
 }

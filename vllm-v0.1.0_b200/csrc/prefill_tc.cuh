@@ -43,7 +43,26 @@ struct PrefillParams {
   int32_t head_size;
   float scale_log2;
   float* dbg;          // tests: raw S of the first tile, raw O, row sums / maxima of tile A of CTA (0, 0)
+  // kPaged: keys / values come straight from the paged caches (tiles.ktok0 then holds the sequence index)
+  const void* key_cache;        // [block][head][head_size / 8][block_size][8]
+  const void* value_cache;      // [block][head][head_size][block_size]
+  const int32_t* block_tables;  // [sequence][max_blocks]
+  int32_t max_blocks;
+  int32_t block_shift;          // log2(block_size): 3, 4 or 5
 };
+
+constexpr int kPfPageThreads = 96;   // warps 8, 10 and 11 copy pages when kPaged
+
+// 16 bytes global -> shared, the last 16 - src_bytes of them zero-filled (Ampere-style async copy: any
+// destination address per thread, which is what turns a cache page into a swizzled operand tile)
+__device__ __forceinline__ void cp_async16(uint32_t dst, const void* src, int src_bytes) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" :: "r"(dst), "l"(src), "r"(src_bytes) : "memory");
+}
+// the mbarrier receives one arrival (of its expected count) when all of this thread's earlier cp.async have completed
+__device__ __forceinline__ void cp_async_arrive(uint32_t bar) {
+  asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" :: "r"(bar) : "memory");
+}
+
 
 __device__ __forceinline__ float ex2(float x) {   // exp2(-inf) == 0
   float y;
@@ -81,7 +100,7 @@ __device__ __forceinline__ void fadd2(float& a0, float& a1, float b0, float b1) 
 __device__ __forceinline__ void named_sync(int id) { asm volatile("bar.sync %0, 256;" :: "r"(id) : "memory"); }
 __device__ __forceinline__ void named_arrive(int id) { asm volatile("bar.arrive %0, 256;" :: "r"(id) : "memory"); }
 
-template <typename T, int DP>
+template <typename T, int DP, bool kPaged = false>
 __global__ void __launch_bounds__(kPfThreads, 1)
 prefill_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant__ CUtensorMap tmk,
                   const __grid_constant__ CUtensorMap tmv, const __grid_constant__ PrefillTiles tiles,
@@ -93,7 +112,10 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant
   constexpr uint32_t kIdescQK = tc05::instr_desc_f16(kBf16, 128, 128, false, false);
   // head sizes 80 and 96 ride in the 128-wide tiles (TMA zero-fills the padding) but only their own
   // k-steps of Q.K^T and their own N columns of P.V are issued
-  const uint32_t idesc_pv = tc05::instr_desc_f16(kBf16, 128, p.head_size, false, true);
+  // V is the B operand of P.V: packed rows give an MN-major tile ([token][d]); cache pages give a K-major one
+  // ([d][token], the page's own order)
+  const uint32_t idesc_pv = tc05::instr_desc_f16(kBf16, 128, p.head_size, false, !kPaged);
+  constexpr uint32_t kVAtomBytes = DP * 128;     // kPaged: 64 tokens (128 bytes) of every d row
   const int qk_steps = p.head_size / 16;
   constexpr uint32_t kTmS = 0, kTmO = 256, kTmCols = 512;   // S_i at 128 i, O_i at 256 + 128 i
 
@@ -124,8 +146,8 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant
     tc05::tma_prefetch_desc(&tmq); tc05::tma_prefetch_desc(&tmk); tc05::tma_prefetch_desc(&tmv);
     mbar_init(bar_q, 1);
     for (int s = 0; s < 2; ++s) {
-      mbar_init(bar_kf + 8 * s, 1); mbar_init(bar_ke + 8 * s, 1);
-      mbar_init(bar_vf + 8 * s, 1); mbar_init(bar_ve + 8 * s, 1);
+      mbar_init(bar_kf + 8 * s, kPaged ? kPfPageThreads : 1); mbar_init(bar_ke + 8 * s, 1);
+      mbar_init(bar_vf + 8 * s, kPaged ? kPfPageThreads : 1); mbar_init(bar_ve + 8 * s, 1);
       mbar_init(bar_s + 8 * s, 1); mbar_init(bar_p + 8 * s, 128); mbar_init(bar_o + 8 * s, 1);
     }
     asm volatile("st.shared.f32 [%0], %1;" :: "r"(sc_slot), "f"(p.scale_log2) : "memory");
@@ -138,7 +160,101 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant
   uint32_t tmem;
   asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem) : "r"(tm_slot) : "memory");
 
-  if (warp == 8) {
+  if (kPaged && (warp == 8 || warp >= 10)) {
+    // ===================== page producer (kPaged) =====================
+    // Three warps copy the K and V pages of the sequence into the operand tiles.  As 16-byte chunks a K page
+    // ([d / 8][token][8]) and a V page ([d][token]) are permutations of the 128-byte-swizzled K-major tiles
+    // tcgen05.mma reads (K: row = token, chunk = d / 8; V: row = d, chunk = token / 8), so every thread moves
+    // chunks with cp.async to the address the swizzle dictates: global reads stay page-contiguous, no gather
+    // pass, no scratch.  Tokens past the context are zero-filled by the copy itself (never-written slots of the
+    // last page may hold anything; 0 x NaN must not reach O).  Nobody waits for a copy: each thread hangs an
+    // arrival on the tile's full-barrier behind its copies (cp.async.mbarrier.arrive.noinc) and moves on to the
+    // next free stage, so up to the whole ring is in flight; the issuer crosses to the async proxy with a proxy
+    // fence after its barrier wait.
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 56;");
+    const int pt = (warp == 8 ? 0 : warp - 9) * 32 + lane;          // 0 .. 95
+    if (pt == 0) {
+      mbar_expect_tx(bar_q, (nB ? 2 : 1) * kTileBytes);
+#pragma unroll
+      for (int a = 0; a < kAtoms; ++a) tc05::tma_load_3d(sQ + a * kAtomBytes, &tmq, a * 64, head, qtok0 + q0, bar_q);
+      if (nB) {
+#pragma unroll
+        for (int a = 0; a < kAtoms; ++a)
+          tc05::tma_load_3d(sQ + kTileBytes + a * kAtomBytes, &tmq, a * 64, head, qtok0 + q0 + 128, bar_q);
+      }
+    }
+    const int shB = p.block_shift, B = 1 << shB;
+    const int D = p.head_size;
+    const int64_t page_bytes = static_cast<int64_t>(D) * B * 2;
+    const int64_t block_stride = page_bytes * p.num_heads, head_off = page_bytes * head;
+    const int32_t* table = p.block_tables + static_cast<int64_t>(ktok0) * p.max_blocks;   // ktok0 = sequence index
+    const char* kc = static_cast<const char*>(p.key_cache);
+    const char* vc = static_cast<const char*>(p.value_cache);
+    const int npg = kPfCols >> shB;                 // pages per 128-token tile
+    const int kchunks = (D >> 3) << shB;            // 16-byte chunks of a K page, of a V page likewise
+    // block numbers of a tile's pages: lane l fetches page l's (one coalesced load per warp, issued a tile ahead
+    // so its latency hides behind the copies of the current tile), the page loops read them by shuffle
+    auto tile_blocks = [&](int t) {
+      const int ptok = t * kPfCols + (lane << shB);
+      return (lane < npg && ptok < klen) ? __ldg(table + (ptok >> shB)) : 0;
+    };
+    // The producer warps share their schedulers with the softmax warps, so instructions per copy are what
+    // counts: everything that does not depend on the page (the chunk's place in the page, its swizzled place
+    // in the tile) is computed once per thread-chunk, the page loop inside adds the page's base and copies.
+    const int iters = (kchunks + kPfPageThreads - 1) / kPfPageThreads;
+    auto load_k = [&](int t, uint32_t dst, int blocks) {
+      const int nvalid = klen - t * kPfCols;        // tokens of this tile inside the context
+      for (int i = 0; i < iters; ++i) {
+        const int idx = pt + i * kPfPageThreads;
+        const bool mine = idx < kchunks;
+        const int c = idx >> shB, tl = idx & (B - 1);
+        // row r = page * B + tl: r & 7 == tl & 7 (B is a multiple of 8), so the swizzle term is page-invariant
+        uint32_t d = dst + (c >> 3) * kAtomBytes + tl * 128 + (((c & 7) ^ (tl & 7)) << 4);
+        const char* src = kc + head_off + idx * 16;
+        int left = nvalid - tl;                     // > 0: this token of page 0 is inside the context
+#pragma unroll 4
+        for (int pg = 0; pg < npg; ++pg) {
+          const int64_t page = static_cast<int64_t>(__shfl_sync(0xffffffffu, blocks, pg)) * block_stride;
+          if (mine) cp_async16(d, src + page, left > 0 ? 16 : 0);
+          d += B * 128;
+          left -= B;
+        }
+      }
+    };
+    auto load_v = [&](int t, uint32_t dst, int blocks) {
+      const int shC = shB - 3;                      // log2(8-token chunks per d row of a page)
+      const int nvalid = klen - t * kPfCols;
+      for (int i = 0; i < iters; ++i) {
+        const int idx = pt + i * kPfPageThreads;
+        const bool mine = idx < kchunks;
+        const int d = idx >> shC, tcl = idx & ((1 << shC) - 1);
+        const uint32_t drow = dst + d * 128;
+        const char* src = vc + head_off + idx * 16;
+        int tc = tcl;                               // 8-token chunk of the tile: page * (B / 8) + tcl
+#pragma unroll 4
+        for (int pg = 0; pg < npg; ++pg) {
+          const int64_t page = static_cast<int64_t>(__shfl_sync(0xffffffffu, blocks, pg)) * block_stride;
+          const int nv = min(max(nvalid - tc * 8, 0), 8);
+          if (mine) cp_async16(drow + (tc >> 3) * kVAtomBytes + (((tc & 7) ^ (d & 7)) << 4), src + page, nv * 2);
+          tc += 1 << shC;
+        }
+      }
+    };
+    int next_blocks = tile_blocks(0);
+    for (int j = 0; j < nmax; ++j) {
+      const int s = j & 1;
+      const uint32_t ph = ((j >> 1) & 1) ^ 1;
+      const int blocks = next_blocks;
+      if (j + 1 < nmax) next_blocks = tile_blocks(j + 1);
+      mbar_wait(bar_ke + 8 * s, ph);
+      load_k(j, sK + s * kTileBytes, blocks);
+      cp_async_arrive(bar_kf + 8 * s);              // arrives by itself once this thread's copies have landed
+      mbar_wait(bar_ve + 8 * s, ph);
+      load_v(j, sV + s * kTileBytes, blocks);
+      cp_async_arrive(bar_vf + 8 * s);
+    }
+    asm volatile("cp.async.wait_all;" ::: "memory");   // nothing of this thread's may be in flight when the CTA exits
+  } else if (warp == 8) {
     // ===================== TMA producer =====================
     asm volatile("setmaxnreg.dec.sync.aligned.u32 56;");
     if (lane == 0) {
@@ -177,12 +293,15 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant
       auto issue_pv = [&](int i, int j) {           // O_i (+)= P_i . V_j
         const uint32_t vb = sV + (j & 1) * kTileBytes;
 #pragma unroll
-        for (int kk = 0; kk < kPfCols / 16; ++kk)
-          tc05::mma_ts(tmem + kTmO + 128 * i, tmem + kTmS + 128 * i + kk * 8,
-                       tc05::smem_desc_sw128(vb + kk * 2048, kAtomBytes, 1024), idesc_pv, j > 0 || kk > 0);
+        for (int kk = 0; kk < kPfCols / 16; ++kk) {
+          const uint64_t vdesc = kPaged ? tc05::smem_desc_sw128(vb + (kk >> 2) * kVAtomBytes + (kk & 3) * 32, 16, 1024)
+                                        : tc05::smem_desc_sw128(vb + kk * 2048, kAtomBytes, 1024);
+          tc05::mma_ts(tmem + kTmO + 128 * i, tmem + kTmS + 128 * i + kk * 8, vdesc, idesc_pv, j > 0 || kk > 0);
+        }
       };
       mbar_wait(bar_q, 0);
       mbar_wait(bar_kf, 0);
+      if (kPaged) tc05::fence_async_smem();         // cp.async wrote through the generic proxy
       tc05::fence_after_sync();
       issue_qk(0, 0);
       tc05::mma_commit(bar_s);
@@ -193,6 +312,7 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant
         const bool more_k = j + 1 < nmax;
         if (more_k) { mbar_wait(bar_kf + 8 * (s ^ 1), ((j + 1) >> 1) & 1); }
         mbar_wait(bar_vf + 8 * s, (j >> 1) & 1);
+        if (kPaged) tc05::fence_async_smem();
 #pragma unroll
         for (int i = 0; i < 2; ++i) {
           const int ni = i ? nB : nA;
