@@ -139,7 +139,7 @@ static int launch_tc(const CUtensorMap& mq, const CUtensorMap& mk, const CUtenso
   constexpr int smem = 6 * (DP / 64) * 128 * 128 + 1024 + 128;
   auto kern = prefill_tc_kernel<T, DP, kPaged>;
   PA_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-  kern<<<dim3(p.num_heads, ntiles), kPfThreads, smem, stream>>>(mq, mk, mv, tiles, p);
+  kern<<<p.tile_major ? dim3(ntiles, p.num_heads) : dim3(p.num_heads, ntiles), kPfThreads, smem, stream>>>(mq, mk, mv, tiles, p);
   count_launch();
   return check_cuda(cudaGetLastError(), "prefill_tc_kernel launch");
 }
@@ -216,6 +216,8 @@ static int prefill(void* out, const void* query, const void* key, const void* va
   PrefillParams p;
   p.out = out; p.out_stride = out_stride; p.num_heads = num_heads; p.head_size = head_size;
   p.scale_log2 = scale * 1.4426950408889634f; p.dbg = dbg;
+  // K/V bytes of the batch against the L2 (126 MB on B200): beyond it, query tiles of one head run together
+  p.tile_major = ktok * num_heads * head_size * 4 > (int64_t{96} << 20);
   p.key_cache = nullptr; p.value_cache = nullptr; p.block_tables = nullptr; p.max_blocks = 0; p.block_shift = 0;
   if (paged) {
     p.key_cache = paged->key_cache; p.value_cache = paged->value_cache; p.block_tables = paged->block_tables;
