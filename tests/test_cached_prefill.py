@@ -230,3 +230,32 @@ def test_untouched_rows_unwritten_slots_and_errors():
     # nothing to do
     attention_ops.multi_query_cached_kv_attention([0], out, qkv[:, 0], kc.to(dev), vc.to(dev), c["scale"],
                                                   c["block_tables"][:0].to(dev), [], 16)
+
+
+@pytest.mark.gpu
+def test_grid_order_does_not_change_results():
+    """Same property for the paged kernel: 6 chunks over 4000-token contexts, 10 heads (123 MB of K/V: tiles fastest)
+    against the same sequences in two calls of 3 (heads fastest), bit for bit."""
+    from vllm_b200 import attention_ops
+    dtype, h, d, b = torch.float16, 10, 128, 16
+    pairs = [(700, 4000), (1, 4000), (4000, 4000), (333, 4096), (2048, 4000), (129, 3900)]
+    assert sum(p[1] for p in pairs) * h * d * 4 > 96 << 20
+    c = _random_problem(dtype, d, b, pairs, h=h, seed=21)
+    dev = "cuda"
+    q = c["qkv"].to(dev)[:, 0]
+    kc, vc, bt = c["key_cache"].to(dev), c["value_cache"].to(dev), c["block_tables"].to(dev)
+    cu, ctx = c["cu_query_lens"], [p[1] for p in pairs]
+    whole = torch.empty(q.shape, dtype=dtype, device=dev)
+    attention_ops.multi_query_cached_kv_attention(cu, whole, q, kc, vc, c["scale"], bt, ctx, b)
+    parts = torch.empty_like(whole)
+    for lo, hi in ((0, 3), (3, 6)):
+        sub_cu = [v - cu[lo] for v in cu[lo:hi + 1]]
+        attention_ops.multi_query_cached_kv_attention(sub_cu, parts[cu[lo]:cu[hi]], q[cu[lo]:cu[hi]], kc, vc, c["scale"],
+                                                      bt[lo:hi].contiguous(), ctx[lo:hi], b)
+    torch.cuda.synchronize()
+    assert torch.equal(whole.view(torch.int16), parts.view(torch.int16))
+    # the one-token and the 129-token chunks against the fp32 oracle
+    for i in (1, 5):
+        truth = paged_oracle.cached_prefill_attention_fp32([0, pairs[i][0]], c["query"][cu[i]:cu[i + 1]], c["key_cache"],
+                                                           c["value_cache"], c["block_tables"][i:i + 1], [ctx[i]], c["scale"])
+        _close(whole[cu[i]:cu[i + 1]].cpu(), truth, dtype, f"chunk {i}")

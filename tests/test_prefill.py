@@ -173,3 +173,30 @@ def test_prefill_padding_tokens_untouched_and_errors():
                                                bad[:, 1], bad[:, 2], [8], 1.0)
     # nothing to do
     attention_ops.multi_query_kv_attention(out, qkv[:, 0], qkv[:, 1], qkv[:, 2], [], 1.0)
+
+
+@pytest.mark.gpu
+def test_prefill_grid_order_does_not_change_results():
+    """A batch whose K/V exceeds L2 runs with tiles fastest in the grid, a smaller one with heads fastest
+    (prefill_attention.cu: tile_major).  Prompts are independent, so one call over 8 prompts (114 MB of K/V)
+    must equal, bit for bit, two calls over 4 prompts each (57 MB) -- and a sample of rows must match the oracle."""
+    from vllm_b200 import attention_ops
+    dtype, h, d = torch.bfloat16, 8, 128
+    lens = [3500, 3400, 3600, 3500, 3300, 3700, 3500, 3500]
+    n = sum(lens)
+    g = torch.Generator(device="cuda").manual_seed(11)
+    qkv = torch.empty((n, 3, h, d), dtype=dtype, device="cuda").normal_(generator=g)
+    scale = d ** -0.5
+    whole = torch.empty((n, h, d), dtype=dtype, device="cuda")
+    attention_ops.multi_query_kv_attention(whole, qkv[:, 0], qkv[:, 1], qkv[:, 2], lens, scale)
+    parts = torch.empty_like(whole)
+    half = sum(lens[:4])
+    attention_ops.multi_query_kv_attention(parts[:half], qkv[:half, 0], qkv[:half, 1], qkv[:half, 2], lens[:4], scale)
+    attention_ops.multi_query_kv_attention(parts[half:], qkv[half:, 0], qkv[half:, 1], qkv[half:, 2], lens[4:], scale)
+    torch.cuda.synchronize()
+    assert torch.equal(whole.view(torch.int16), parts.view(torch.int16))
+    # the last prompt against the fp32 oracle (one prompt keeps the CPU side quick)
+    start = n - lens[-1]
+    last = qkv[start:].cpu()
+    truth = paged_oracle.prefill_attention_fp32([lens[-1]], last[:, 0], last[:, 1], last[:, 2], scale)
+    _close(whole[start:].cpu(), truth, dtype, "last prompt of the large batch")
