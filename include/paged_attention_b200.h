@@ -145,10 +145,14 @@ PA_API int pa_decode_attention(void* out, const void* query, const void* key_cac
 /* Launch-shape overrides for tuning and tests; 0 / negative = automatic. */
 typedef struct pa_decode_tuning {
   int32_t variant;    /* 0 auto, 1 direct global loads, 2 bulk-copy staged (sibling groups
-                         served together), 3 bulk-copy staged without sibling groups */
-  int32_t num_warps;  /* warps per CTA working on one (seq, head, split)     */
-  int32_t num_stages; /* pages in flight per warp (variant 2)                */
-  int32_t num_splits; /* context partitions per (seq, head)                  */
+                         served together), 3 bulk-copy staged without sibling groups,
+                         4 persistent work queue: one CTA per SM, warps pull (seq, head,
+                         chunk of pages) units from a counter, rings never drain */
+  int32_t num_warps;  /* warps per CTA working on one (seq, head, split); variant 4: independent
+                         warps per SM                                         */
+  int32_t num_stages; /* pages in flight per warp (variants 2-4)             */
+  int32_t num_splits; /* context partitions per (seq, head); variant 4: chunks a context of
+                         max_context_len tokens is cut into                   */
 } pa_decode_tuning;
 
 /* Same operator with explicit launch shape (tuning == NULL -> automatic). */
@@ -162,7 +166,18 @@ PA_API int pa_decode_attention_ex(void* out, const void* query, const void* key_
                            int32_t dtype, const pa_decode_tuning* tuning,
                            void* stream);
 
-/* The launch shape pa_decode_attention would pick for these sizes. */
+/* Sizes the per-(device, stream) split-context scratch for this shape without launching anything, so a
+ * later pa_decode_attention call of that shape never allocates -- required before capturing the call into
+ * a CUDA graph (growing the scratch synchronises the stream, which capture forbids; the call then fails
+ * with PA_ERR_INVALID_ARGUMENT instead). */
+PA_API int pa_decode_attention_reserve(int32_t num_seqs, int32_t num_heads,
+                                int32_t head_size, int32_t block_size,
+                                int32_t max_num_blocks_per_seq,
+                                int32_t max_context_len, int32_t dtype,
+                                const pa_decode_tuning* tuning, void* stream);
+
+/* The launch shape pa_decode_attention would pick for these sizes (plan_out->variant selects the
+ * kernel family on entry; 0 = automatic). */
 PA_API int pa_decode_attention_plan(int32_t num_seqs, int32_t num_heads,
                              int32_t head_size, int32_t block_size,
                              int32_t max_context_len, int32_t dtype,

@@ -70,6 +70,50 @@ def attention_case(case_id: str) -> Dict[str, object]:
     }
 
 
+def attention_large_case_ids() -> List[str]:
+    """BASELINE.json configs[0] exactly as the reference test builds it, and one long-context case per dtype
+    and input distribution (the small cases above stop at 180 tokens)."""
+    return ["cfg1-f32-ref"] + [f"{dt}-long-{dist}" for dt in DTYPES for dist in ("ref", "unit")]
+
+
+def attention_large_case(case_id: str) -> Dict[str, object]:
+    """cfg1-f32-ref: 7 sequences x 40 heads x 128, block 16, 1024 blocks, fp32, values U(-1e-3, 1e-3), context
+    lengths and block tables drawn from Python's `random` seeded with 0 in the order the reference test draws
+    them (tests/kernels/test_attention.py:183-195: all lengths in [1, 4096] first, then one row of
+    ceil(max/16) block numbers in [0, 1023] per sequence -- rows are longer than most contexts need and blocks
+    repeat within and across sequences).
+    {dt}-long-{dist}: 3 sequences x 2 heads x 128, block 16, contexts 4096 / 4090 / 3000 over 320 blocks."""
+    import random
+    seed = int(hashlib.sha256(("large-" + case_id).encode()).hexdigest()[:8], 16)
+    rs = np.random.RandomState(seed)
+    if case_id == "cfg1-f32-ref":
+        dtype, dist = torch.float32, "ref"
+        num_seqs, num_heads, head_size, block_size, num_blocks = 7, 40, 128, 16, 1024
+        rnd = random.Random(0)
+        ctx = [rnd.randint(1, 4096) for _ in range(num_seqs)]
+        max_blocks = (max(ctx) + block_size - 1) // block_size
+        tables = np.array([[rnd.randint(0, num_blocks - 1) for _ in range(max_blocks)] for _ in range(num_seqs)],
+                          dtype=np.int32)
+    else:
+        dt, _, dist = case_id.split("-")
+        dtype = DTYPES[dt]
+        num_seqs, num_heads, head_size, block_size, num_blocks = 3, 2, 128, 16, 320
+        ctx = [4096, 4090, 3000]
+        max_blocks = (max(ctx) + block_size - 1) // block_size
+        tables = rs.randint(0, num_blocks, size=(num_seqs, max_blocks)).astype(np.int32)
+    x = 16 // torch.empty((), dtype=dtype).element_size()
+    qkv = _tensor(rs, (num_seqs, 3, num_heads, head_size), dtype, dist)
+    key_cache = _tensor(rs, (num_blocks, num_heads, head_size // x, block_size, x), dtype, dist)
+    value_cache = _tensor(rs, (num_blocks, num_heads, head_size, block_size), dtype, dist)
+    return {
+        "dtype": dtype, "block_size": block_size, "head_size": head_size, "num_heads": num_heads,
+        "scale": float(1.0 / (head_size ** 0.5)),
+        "query": qkv[:, 0], "key_cache": key_cache, "value_cache": value_cache,
+        "block_tables": torch.from_numpy(tables), "context_lens": torch.tensor(ctx, dtype=torch.int32),
+        "max_context_len": max(ctx),
+    }
+
+
 def cache_case_ids() -> List[str]:
     return [f"{dt}-b{b}-d{d}" for dt in DTYPES for (b, d) in ((8, 16), (16, 64), (32, 128), (16, 80))]
 

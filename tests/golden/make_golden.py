@@ -77,6 +77,24 @@ def make_attention() -> None:
     json.dump(meta, open(os.path.join(HERE, "attention_inputs.sha256.json"), "w"), indent=1, sort_keys=True)
 
 
+def make_attention_large() -> None:
+    """BASELINE.json configs[0] (the reference test's own shape and procedure) and the long-context cases."""
+    ns = _functions(os.path.join(REF, "tests/kernels/test_attention.py"),
+                    {"ref_masked_attention", "ref_single_query_cached_kv_attention"})
+    ref = ns["ref_single_query_cached_kv_attention"]
+    out, meta = {}, {}
+    for cid in cases.attention_large_case_ids():
+        c = cases.attention_large_case(cid)
+        o = torch.empty_like(c["query"])
+        with torch.inference_mode():
+            ref(o, c["query"], c["key_cache"], c["value_cache"], c["block_tables"], c["context_lens"])
+        out[cid] = cases.to_numpy(o)
+        meta[cid] = cases.digest(c["query"], c["key_cache"], c["value_cache"], c["block_tables"], c["context_lens"])
+        print(cid, float(o.float().abs().max()))
+    np.savez_compressed(os.path.join(HERE, "attention_golden_large.npz"), **out)
+    json.dump(meta, open(os.path.join(HERE, "attention_large_inputs.sha256.json"), "w"), indent=1, sort_keys=True)
+
+
 def make_cache() -> None:
     path = os.path.join(REF, "tests/kernels/test_cache.py")
     loop_copy = _reference_loop(path, "run_copy_blocks")
@@ -223,9 +241,11 @@ def make_cached_prefill() -> None:
 
 if __name__ == "__main__":
     torch.manual_seed(0)
-    which = sys.argv[1:] or ["attention", "cache", "rope", "prefill", "cached_prefill"]
+    which = sys.argv[1:] or ["attention", "attention_large", "cache", "rope", "prefill", "cached_prefill"]
     if "attention" in which:
         make_attention()
+    if "attention_large" in which:
+        make_attention_large()
     if "cache" in which:
         make_cache()
     if "rope" in which:

@@ -40,6 +40,8 @@ def test_golden_reference_outputs(cid, variant):
     gold = cases.from_numpy(att[cid], c["dtype"])
     # tolerance of the north star (1e-3 fp16, 1e-2 bf16), relative to the output scale
     pt.assert_decode_close(got, gold, c["dtype"], f"{cid} v{variant} vs reference output")
+    # the north star's tolerance flat (atol = rtol = 1e-3 fp16 / 1e-2 bf16), not scaled by the output magnitude
+    pt.assert_flat_north_star(got, gold, c["dtype"], f"{cid} v{variant}")
     # and by the letter of the reference test (atol=1e-3, rtol=1e-5; test_attention.py:224)
     if cid.endswith("-ref"):
         assert torch.allclose(got.float().cpu(), gold.float(), atol=1e-3, rtol=1e-5)
@@ -47,6 +49,29 @@ def test_golden_reference_outputs(cid, variant):
     cq = pt.DecodeProblem(c["query"], c["key_cache"], c["value_cache"], c["block_tables"], c["context_lens"],
                           c["scale"], c["block_size"], c["max_context_len"])
     pt.assert_decode_close(got, pt.oracle_decode(cq), c["dtype"], f"{cid} v{variant} vs C oracle")
+
+
+@pytest.mark.parametrize("variant", [0, 1, 2, 4])
+@pytest.mark.parametrize("cid", cases.attention_large_case_ids())
+def test_large_goldens_config1_and_long_contexts(cid, variant):
+    """BASELINE.json configs[0] as the reference test builds it (7 x 40 x 128, block 16, fp32, 1024 aliasing
+    blocks, contexts <= 4096 from random.seed(0)) and 4096-token contexts per dtype, against outputs of the
+    reference's own function at those sizes (tests/golden/attention_golden_large.npz)."""
+    att = np.load(os.path.join(GOLD, "attention_golden_large.npz"))
+    c = cases.attention_large_case(cid)
+    qkv = c["query"]._base.to(DEV)
+    p = pt.DecodeProblem(qkv[:, 0], c["key_cache"].to(DEV), c["value_cache"].to(DEV), c["block_tables"].to(DEV),
+                         c["context_lens"].to(DEV), c["scale"], c["block_size"], c["max_context_len"])
+    got = pt.run_decode(p, tuning=pt.tuning(variant=variant))
+    gold = cases.from_numpy(att[cid], c["dtype"])
+    pt.assert_decode_close(got, gold, c["dtype"], f"{cid} v{variant} vs reference output")
+    pt.assert_flat_north_star(got, gold, c["dtype"], f"{cid} v{variant}")
+    if cid.endswith("-ref"):
+        # the reference test's own tolerance (test_attention.py:224)
+        assert torch.allclose(got.float().cpu(), gold.float(), atol=1e-3, rtol=1e-5)
+    if c["dtype"] == torch.float32:
+        # fp32 is held to 1e-4 relative to the output scale on top of the letter
+        assert float((got.float().cpu() - gold.float()).abs().max()) <= 1e-4 * float(gold.float().abs().max())
 
 
 # ---------------------------------------------------------------------------

@@ -65,6 +65,51 @@ def test_fp32_and_c_oracles_match_reference_output(cid):
                                rtol={torch.float16: 2e-3, torch.bfloat16: 1.6e-2, torch.float32: 2e-5}[c["dtype"]])
 
 
+ATT_LARGE = np.load(os.path.join(GOLD, "attention_golden_large.npz"))
+ATT_LARGE_SHA = json.load(open(os.path.join(GOLD, "attention_large_inputs.sha256.json")))
+
+
+@pytest.mark.parametrize("cid", cases.attention_large_case_ids())
+def test_large_cases_config1_and_long_contexts(cid):
+    """BASELINE.json configs[0] (7 x 40 x 128, fp32, contexts <= 4096, the reference test's own procedure) and
+    4096-token contexts per dtype: both oracles against outputs of the reference's function at those sizes."""
+    c = cases.attention_large_case(cid)
+    assert cases.digest(c["query"], c["key_cache"], c["value_cache"], c["block_tables"], c["context_lens"]) == ATT_LARGE_SHA[cid]
+    if cid.startswith("cfg1"):
+        assert c["query"].shape == (7, 40, 128) and c["key_cache"].shape == (1024, 40, 32, 16, 4)
+        assert c["dtype"] == torch.float32 and int(c["context_lens"].max()) <= 4096
+    gold = cases.from_numpy(ATT_LARGE[cid], c["dtype"]).float()
+    scale = float(gold.abs().max())
+    tol = TRUTH_TOL[c["dtype"]]
+    cout = torch.empty(c["query"].shape, dtype=c["dtype"])
+    c_oracle.decode_attention(cout, c["query"].contiguous(), c["key_cache"], c["value_cache"], c["scale"],
+                              c["block_tables"], c["context_lens"])
+    sub = 1.2e-7 if c["dtype"] == torch.float16 else 0.0     # two fp16 subnormal steps (outputs ~4e-5 are subnormal)
+    torch.testing.assert_close(cout.float(), gold, atol=tol * scale + sub, rtol=tol)
+    # by the letter of the reference test (test_attention.py:224) and of the north star
+    assert torch.allclose(cout.float(), gold, atol=1e-3, rtol=1e-5) or not cid.endswith("-ref")
+    flat = {torch.float16: 1e-3, torch.bfloat16: 1e-2, torch.float32: 1e-3}[c["dtype"]]
+    torch.testing.assert_close(cout.float(), gold, atol=flat, rtol=flat)
+    truth = paged_oracle.decode_attention_fp32(c["query"], c["key_cache"], c["value_cache"], c["block_tables"],
+                                               c["context_lens"], c["scale"])
+    torch.testing.assert_close(truth, gold, atol=tol * scale + sub, rtol=tol)
+
+
+def test_flat_north_star_tolerance_holds_for_the_oracle_on_unit_scale_goldens():
+    """The unit-scale goldens (outputs of the reference function in the input dtype) against the C oracle under
+    the flat tolerance the north star states -- the same check the GPU tests apply to the kernels."""
+    for cid in cases.attention_case_ids():
+        if not cid.endswith("-unit"):
+            continue
+        c = cases.attention_case(cid)
+        gold = cases.from_numpy(ATT[cid], c["dtype"]).float()
+        cout = torch.empty(c["query"].shape, dtype=c["dtype"])
+        c_oracle.decode_attention(cout, c["query"].contiguous(), c["key_cache"], c["value_cache"], c["scale"],
+                                  c["block_tables"], c["context_lens"])
+        flat = {torch.float16: 1e-3, torch.bfloat16: 1e-2, torch.float32: 1e-3}[c["dtype"]]
+        torch.testing.assert_close(cout.float(), gold, atol=flat, rtol=flat, msg=lambda m: f"{cid}: {m}")
+
+
 def test_zero_context_is_zero_output():
     c = cases.attention_case("f32-b16-d64-ref")
     lens = c["context_lens"].clone()

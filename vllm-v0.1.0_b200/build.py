@@ -23,8 +23,8 @@ LIBDIR = os.path.join(HERE, "lib")
 LIB = os.path.join(LIBDIR, "libpaged_b200.so")
 
 SOURCES = ["pa_api.cu", "cache_movers.cu", "step_tables.cu", "probe.cu", "prefill_attention.cu", "allreduce.cu", "decode_f16.cu", "decode_bf16.cu", "decode_f32.cu"]
-HEADERS = [os.path.join(CSRC, "pa_common.cuh"), os.path.join(CSRC, "decode_attention.cuh"), os.path.join(CSRC, "tc05.cuh"), os.path.join(CSRC, "prefill_tc.cuh"),
-           os.path.join(ROOT, "include", "paged_attention_b200.h")]
+ABI_HEADER = os.path.join(ROOT, "include", "paged_attention_b200.h")
+HEADERS = sorted(os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".cuh", ".h"))) + [ABI_HEADER]
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",
@@ -78,7 +78,8 @@ def build_torch_binding(force: bool = False) -> str:
     from torch.utils import cpp_extension as ce
     src = os.path.join(CSRC, "torch_binding.cpp")
     stamp = TORCH_OPS + ".sha"
-    want = _digest([src, HEADERS[2]]) + torch.__version__
+    # the binding is rebuilt whenever the C ABI header or the library it links changes
+    want = _digest([src, ABI_HEADER, LIB]) + torch.__version__
     if not force and os.path.exists(TORCH_OPS) and os.path.exists(stamp) and open(stamp).read() == want:
         return TORCH_OPS
     cxx = "/usr/bin/g++" if os.path.exists("/usr/bin/g++") else (shutil.which("g++") or "g++")
@@ -116,7 +117,26 @@ def build(force: bool = False, verbose: bool = False) -> str:
         if r.returncode != 0:
             raise RuntimeError(f"link failed:\n{r.stdout}\n{r.stderr}")
     build_torch_binding(force)
+    print(f"[build] {os.path.relpath(LIB, ROOT)} sha256 {_digest([LIB])[:16]} built from sources {source_digest()[:16]}",
+          file=sys.stderr)
     return LIB
+
+
+def source_digest() -> str:
+    """Digest of every source the library is compiled from (flags included): printed by build() so a
+    stale lib/*.so on the GPU box is visible in the log."""
+    return _digest([os.path.join(CSRC, s) for s in SOURCES] + HEADERS + [os.path.join(CSRC, "torch_binding.cpp")])
+
+
+def stale_objects():
+    """Sources whose object stamp does not match (no nvcc needed): empty list = the .so is current."""
+    out = []
+    for src in SOURCES:
+        stamp = os.path.join(BUILD, src.replace(".cu", ".o")) + ".sha"
+        want = _digest([os.path.join(CSRC, src)] + HEADERS)
+        if not (os.path.exists(stamp) and open(stamp).read() == want):
+            out.append(src)
+    return out
 
 
 if __name__ == "__main__":

@@ -236,6 +236,7 @@ struct DecodeParams {
   const int32_t* context_lens;  // [S]
   float* ws_part;             // [S][H][nsplit][D + 2]   (nsplit > 1)
   uint32_t* ws_ticket;        // [S][H], zero between calls (nsplit > 1)
+  uint32_t* ws_ctrl;          // persistent kernel: [0] next dynamic unit, [1] warps that have left; zero between calls
   int64_t q_stride;
   float scale_log2;           // scale * log2(e)
   int32_t num_heads;
@@ -805,6 +806,8 @@ struct DecodeLaunch {
   int32_t block_size;
   int32_t num_warps;
   bool staged;
+  bool persistent;            // work-queue kernel (decode_persistent.cuh): pages_per_split = pages per chunk
+  int32_t grid_ctas;          // persistent: CTAs (one per SM)
   cudaStream_t stream;
 };
 

@@ -10,7 +10,7 @@
 #include <mutex>
 #include <utility>
 
-#include "decode_attention.cuh"
+#include "decode_persistent.cuh"
 
 namespace pa {
 
@@ -37,41 +37,67 @@ void count_launch(uint64_t n) { g_launches.fetch_add(n, std::memory_order_relaxe
 
 // ---------------------------------------------------------------------------
 // per-(device, stream) scratch for split-context partials.
-// Layout: [tickets: items x uint32, padded to 256 B][partials: floats].
-// Tickets are zeroed when the buffer is created and re-armed by the kernel.
+// Layout: [control words: 256 B][tickets: items x uint32, padded to 256 B][partials: floats].
+// Control words and tickets are zeroed when the buffer is created and re-armed by the kernels; after a
+// launch that returned an error they are zeroed again before the next use (an aborted launch may have
+// left them counting).  The buffer only ever grows; growing needs a stream synchronisation, so it is
+// refused while the stream is being captured into a CUDA graph -- size it first with
+// pa_decode_attention_reserve (or one eager call of the same shape).
 // ---------------------------------------------------------------------------
 struct Workspace {
   void* ptr = nullptr;
   size_t bytes = 0;
-  size_t ticket_bytes = 0;
+  size_t ticket_bytes = 0;   // control words included
+  bool dirty = false;
 };
+constexpr size_t kCtrlBytes = 256;
 static std::mutex g_ws_mu;
 static std::map<std::pair<int, cudaStream_t>, Workspace> g_ws;
 
-static int get_workspace(cudaStream_t stream, size_t ticket_bytes, size_t part_bytes, uint32_t** tickets,
-                         float** parts) {
+static int get_workspace(cudaStream_t stream, size_t ticket_bytes, size_t part_bytes, uint32_t** ctrl,
+                         uint32_t** tickets, float** parts) {
   int dev = 0;
   PA_CUDA_TRY(cudaGetDevice(&dev));
   std::lock_guard<std::mutex> lock(g_ws_mu);
   Workspace& w = g_ws[std::make_pair(dev, stream)];
-  ticket_bytes = (ticket_bytes + 255) / 256 * 256;
-  const size_t need = ticket_bytes + part_bytes;
-  if (w.bytes < need || w.ticket_bytes < ticket_bytes || w.bytes - w.ticket_bytes < part_bytes) {
+  ticket_bytes = kCtrlBytes + (ticket_bytes + 255) / 256 * 256;
+  part_bytes = (part_bytes + 255) / 256 * 256;
+  if (w.ticket_bytes < ticket_bytes || w.bytes - w.ticket_bytes < part_bytes) {
+    cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+    PA_CUDA_TRY(cudaStreamIsCapturing(stream, &cap));
+    if (cap != cudaStreamCaptureStatusNone)
+      return set_error(PA_ERR_INVALID_ARGUMENT,
+                       "decode scratch must grow (%zu B) while the stream is being captured: call "
+                       "pa_decode_attention_reserve for this shape before capturing", ticket_bytes + part_bytes);
     if (w.ptr) {
       PA_CUDA_TRY(cudaStreamSynchronize(stream));
       PA_CUDA_TRY(cudaFree(w.ptr));
       w = Workspace();
     }
-    const size_t tb = ticket_bytes * 2;            // head-room: item count may grow
-    const size_t total = tb + (need - ticket_bytes) * 2;
+    const size_t tb = kCtrlBytes + (ticket_bytes - kCtrlBytes) * 2;   // head-room: item count may grow
+    const size_t total = tb + part_bytes * 2;
     PA_CUDA_TRY(cudaMalloc(&w.ptr, total));
     w.bytes = total;
     w.ticket_bytes = tb;
-    PA_CUDA_TRY(cudaMemsetAsync(w.ptr, 0, tb, stream));
+    w.dirty = true;
   }
-  *tickets = static_cast<uint32_t*>(w.ptr);
+  if (w.dirty) {
+    PA_CUDA_TRY(cudaMemsetAsync(w.ptr, 0, w.ticket_bytes, stream));
+    w.dirty = false;
+  }
+  *ctrl = static_cast<uint32_t*>(w.ptr);
+  *tickets = reinterpret_cast<uint32_t*>(static_cast<char*>(w.ptr) + kCtrlBytes);
   *parts = reinterpret_cast<float*>(static_cast<char*>(w.ptr) + w.ticket_bytes);
   return PA_OK;
+}
+
+// a launch on `stream` failed: its control words / tickets may be left counting
+static void poison_workspace(cudaStream_t stream) {
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) return;
+  std::lock_guard<std::mutex> lock(g_ws_mu);
+  auto it = g_ws.find(std::make_pair(dev, stream));
+  if (it != g_ws.end()) it->second.dirty = true;
 }
 
 // ---------------------------------------------------------------------------
@@ -118,6 +144,75 @@ int decode_smem_bytes(int dtype, int head_size, int block_size, int pages_per_sp
   return o;
 }
 
+
+// bytes of dynamic shared memory of the persistent kernel (same formula as PersistMap)
+int persistent_smem_bytes(int dtype, int head_size, int block_size, int num_seqs, int warps, int stages) {
+  const int es = dtype_size(dtype);
+  const int page = head_size * block_size * es;
+  const int pbuf = ((2 * block_size * es + 15) / 16) * 16;
+  int o = ((num_seqs * 4 + 15) / 16) * 16;
+  o += (((num_seqs + 1) * 4 + 15) / 16) * 16;
+  o += warps * (2 * head_size * es + pbuf);
+  o += warps * stages * 8;
+  o = ((o + 127) / 128) * 128;
+  o += warps * stages * 2 * page;
+  return o;
+}
+
+// Launch shape of the persistent work-queue kernel (variant 4): one CTA per SM of `num_warps` independent
+// warps, `num_stages` (K page + V page) stages per warp, contexts cut into `num_splits` chunks at most
+// (pages per chunk through the pointer).  Sizing rules (sweeps in profiles/r2_sweep_persistent.json):
+// ring bytes per SM near the shared-memory limit; chunks so that every warp sees >= ~8 units, never below
+// 64 KiB of KV per unit (each unit costs a partial + a ticket) and never above 512 KiB (the launch's tail
+// is one unit per warp at one warp's own ring bandwidth).
+static int make_persistent_plan(int num_seqs, int num_heads, int head_size, int block_size,
+                                int max_blocks_per_seq, int max_context_len, int dtype, pa_decode_tuning* t,
+                                int* pages_per_chunk) {
+  if (num_seqs > kPersistMaxSeqs)
+    return set_error(PA_ERR_INVALID_ARGUMENT, "variant 4 holds the batch plan in shared memory: %d sequences > %d",
+                     num_seqs, kPersistMaxSeqs);
+  const int es = dtype_size(dtype);
+  const int stage = 2 * head_size * block_size * es;
+  int max_pages = max_context_len > 0 ? (max_context_len + block_size - 1) / block_size : 1;
+  if (max_blocks_per_seq > 0 && max_pages > max_blocks_per_seq) max_pages = max_blocks_per_seq;
+  const int budget = kMaxSmem - persistent_smem_bytes(dtype, head_size, block_size, num_seqs, 0, 0);
+  const int misc = 2 * head_size * es + ((2 * block_size * es + 15) / 16) * 16;
+  if (t->num_stages <= 0) {
+    t->num_stages = 2;
+    if (t->num_warps <= 0) {
+      int w = budget / (2 * (stage + 8) + misc);
+      t->num_warps = w > 16 ? 16 : (w < 1 ? 1 : w);
+    }
+    int s = (budget / t->num_warps - misc) / (stage + 8);      // spend what is left on ring depth
+    t->num_stages = s > 8 ? 8 : (s < 2 ? 2 : s);
+  } else if (t->num_warps <= 0) {
+    int w = budget / (t->num_stages * (stage + 8) + misc);
+    t->num_warps = w > 16 ? 16 : (w < 1 ? 1 : w);
+  }
+  if (t->num_warps > 16) t->num_warps = 16;
+  if (t->num_stages > 32) t->num_stages = 32;
+  if (persistent_smem_bytes(dtype, head_size, block_size, num_seqs, t->num_warps, t->num_stages) > kMaxSmem)
+    return set_error(PA_ERR_INVALID_ARGUMENT, "launch shape does not fit shared memory (warps %d, stages %d)",
+                     t->num_warps, t->num_stages);
+  if (t->num_splits <= 0) {
+    const double total = static_cast<double>(num_seqs) * num_heads * max_pages * stage;
+    const double workers = static_cast<double>(sm_count()) * t->num_warps;
+    double unit = total / (workers * 8.0);
+    if (unit < 64.0 * 1024) unit = 64.0 * 1024;
+    if (unit > 512.0 * 1024) unit = 512.0 * 1024;
+    int c = static_cast<int>(unit / stage);
+    if (c < 1) c = 1;
+    t->num_splits = (max_pages + c - 1) / c;
+  }
+  if (t->num_splits > max_pages) t->num_splits = max_pages;
+  if (t->num_splits < 1) t->num_splits = 1;
+  const int c = (max_pages + t->num_splits - 1) / t->num_splits;
+  t->num_splits = (max_pages + c - 1) / c;
+  *pages_per_chunk = c;
+  if (static_cast<int64_t>(num_seqs) * num_heads * t->num_splits >= (int64_t{1} << 31) - 4 * 148 * 16)
+    return set_error(PA_ERR_INVALID_ARGUMENT, "too many work units");
+  return PA_OK;
+}
 
 constexpr int kMaxPagesPerSplit = 8192;  // block-table slice kept in shared memory (32 KiB)
 
@@ -197,7 +292,7 @@ static int decode(void* out, const void* query, const void* key_cache, const voi
                   const int32_t* block_tables, const int32_t* context_lens, int32_t num_seqs,
                   int32_t num_heads, int32_t head_size, int32_t block_size, int32_t max_num_blocks_per_seq,
                   int32_t max_context_len, int64_t q_stride, int32_t dtype, const pa_decode_tuning* tuning,
-                  cudaStream_t stream) {
+                  cudaStream_t stream, bool reserve_only = false) {
   int rc = check_shape(head_size, block_size, dtype);
   if (rc != PA_OK) return rc;
   if (num_seqs < 0 || num_heads <= 0 || max_num_blocks_per_seq < 0 || max_context_len < 0)
@@ -205,7 +300,7 @@ static int decode(void* out, const void* query, const void* key_cache, const voi
                      num_seqs, num_heads, max_num_blocks_per_seq, max_context_len);
   if (num_seqs == 0) return PA_OK;
   if (num_seqs > 65535) return set_error(PA_ERR_INVALID_ARGUMENT, "too many sequences: %d (max 65535)", num_seqs);
-  if (!out || !query || !key_cache || !value_cache || !block_tables || !context_lens)
+  if (!reserve_only && (!out || !query || !key_cache || !value_cache || !block_tables || !context_lens))
     return set_error(PA_ERR_INVALID_ARGUMENT, "null pointer");
   if ((reinterpret_cast<uintptr_t>(key_cache) | reinterpret_cast<uintptr_t>(value_cache)) & 15u)
     return set_error(PA_ERR_INVALID_ARGUMENT, "key/value cache must be 16-byte aligned");
@@ -215,9 +310,12 @@ static int decode(void* out, const void* query, const void* key_cache, const voi
 
   pa_decode_tuning t = {0, 0, 0, 0};
   if (tuning) t = *tuning;
-  if (t.variant < 0 || t.variant > 3) return set_error(PA_ERR_INVALID_ARGUMENT, "invalid variant %d", t.variant);
+  if (t.variant < 0 || t.variant > 4) return set_error(PA_ERR_INVALID_ARGUMENT, "invalid variant %d", t.variant);
+  const bool persistent = t.variant == 4;
   int pps = 0;
-  rc = make_plan(num_seqs, num_heads, head_size, block_size, max_context_len, dtype, &t, &pps);
+  rc = persistent ? make_persistent_plan(num_seqs, num_heads, head_size, block_size, max_num_blocks_per_seq,
+                                         max_context_len, dtype, &t, &pps)
+                  : make_plan(num_seqs, num_heads, head_size, block_size, max_context_len, dtype, &t, &pps);
   if (rc != PA_OK) return rc;
 
   DecodeLaunch l;
@@ -234,21 +332,27 @@ static int decode(void* out, const void* query, const void* key_cache, const voi
   p.num_stages = t.num_stages;
   p.q_vec_ok = (reinterpret_cast<uintptr_t>(query) % 16 == 0) && ((q_stride * es) % 16 == 0);
   p.num_seqs = num_seqs;
-  p.group_rows = group_rows_for(t.variant >= 2, t.variant, t.num_warps, num_seqs, dtype, block_size,
+  p.group_rows = persistent ? 1 :
+                 group_rows_for(t.variant >= 2, t.variant, t.num_warps, num_seqs, dtype, block_size,
                                 decode_smem_bytes(dtype, head_size, block_size, pps, t.num_warps, t.num_stages, t.variant >= 2));
-  if (t.num_splits > 1) {
+  if (t.num_splits > 1 || persistent) {
     const size_t items = static_cast<size_t>(num_seqs) * num_heads;
-    rc = get_workspace(stream, items * sizeof(uint32_t), items * t.num_splits * (head_size + 2) * sizeof(float),
-                       &p.ws_ticket, &p.ws_part);
+    const size_t parts = t.num_splits > 1 ? items * t.num_splits * (head_size + 2) * sizeof(float) : 0;
+    rc = get_workspace(stream, t.num_splits > 1 ? items * sizeof(uint32_t) : 0, parts, &p.ws_ctrl, &p.ws_ticket,
+                       &p.ws_part);
     if (rc != PA_OK) return rc;
   }
+  if (reserve_only) return PA_OK;
   l.num_seqs = num_seqs; l.head_size = head_size; l.block_size = block_size;
-  l.num_warps = t.num_warps; l.staged = (t.variant >= 2); l.stream = stream;
+  l.num_warps = t.num_warps; l.staged = (t.variant >= 2); l.persistent = persistent; l.grid_ctas = sm_count();
+  l.stream = stream;
   switch (dtype) {
-    case PA_F16:  return launch_decode_f16(l);
-    case PA_BF16: return launch_decode_bf16(l);
-    default:      return launch_decode_f32(l);
+    case PA_F16:  rc = launch_decode_f16(l); break;
+    case PA_BF16: rc = launch_decode_bf16(l); break;
+    default:      rc = launch_decode_f32(l); break;
   }
+  if (rc != PA_OK) poison_workspace(stream);
+  return rc;
 }
 
 }  // namespace pa
@@ -296,12 +400,22 @@ int pa_decode_attention_ex(void* out, const void* query, const void* key_cache, 
                     static_cast<cudaStream_t>(stream));
 }
 
+int pa_decode_attention_reserve(int32_t num_seqs, int32_t num_heads, int32_t head_size, int32_t block_size,
+                                int32_t max_num_blocks_per_seq, int32_t max_context_len, int32_t dtype,
+                                const pa_decode_tuning* tuning, void* stream) {
+  return pa::decode(nullptr, nullptr, nullptr, nullptr, 1.f, nullptr, nullptr, num_seqs, num_heads, head_size,
+                    block_size, max_num_blocks_per_seq, max_context_len, head_size, dtype, tuning,
+                    static_cast<cudaStream_t>(stream), true);
+}
+
 int pa_decode_attention_plan(int32_t num_seqs, int32_t num_heads, int32_t head_size, int32_t block_size,
                              int32_t max_context_len, int32_t dtype, pa_decode_tuning* plan_out) {
   if (!plan_out) return pa::set_error(PA_ERR_INVALID_ARGUMENT, "plan_out is null");
   int rc = pa::check_shape(head_size, block_size, dtype);
   if (rc != PA_OK) return rc;
   int pps = 0;
+  if (plan_out->variant == 4)
+    return pa::make_persistent_plan(num_seqs, num_heads, head_size, block_size, 0, max_context_len, dtype, plan_out, &pps);
   return pa::make_plan(num_seqs, num_heads, head_size, block_size, max_context_len, dtype, plan_out, &pps);
 }
 

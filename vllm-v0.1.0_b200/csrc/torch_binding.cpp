@@ -274,6 +274,11 @@ void rotary_embedding_neox_reshape_and_cache(torch::Tensor& positions, torch::Te
 
 PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
   namespace py = pybind11;
+  // compiled against one version of the C ABI header; refuse to run against a library built from another
+  if (pa_abi_version() != PA_ABI_VERSION)
+    throw std::runtime_error("pa_torch_ops was compiled for ABI " + std::to_string(PA_ABI_VERSION) +
+                             " but libpaged_b200.so reports " + std::to_string(pa_abi_version()) +
+                             ": rebuild with python vllm-v0.1.0_b200/build.py");
   m.def("single_query_cached_kv_attention", &single_query_cached_kv_attention, py::arg("out"), py::arg("query"),
         py::arg("key_cache"), py::arg("value_cache"), py::arg("scale"), py::arg("block_tables"),
         py::arg("context_lens"), py::arg("block_size"), py::arg("max_context_len"), py::arg("variant") = 0,
