@@ -145,14 +145,10 @@ PA_API int pa_decode_attention(void* out, const void* query, const void* key_cac
 /* Launch-shape overrides for tuning and tests; 0 / negative = automatic. */
 typedef struct pa_decode_tuning {
   int32_t variant;    /* 0 auto, 1 direct global loads, 2 bulk-copy staged (sibling groups
-                         served together), 3 bulk-copy staged without sibling groups,
-                         4 persistent work queue: one CTA per SM, warps pull (seq, head,
-                         chunk of pages) units from a counter, rings never drain */
-  int32_t num_warps;  /* warps per CTA working on one (seq, head, split); variant 4: independent
-                         warps per SM                                         */
-  int32_t num_stages; /* pages in flight per warp (variants 2-4)             */
-  int32_t num_splits; /* context partitions per (seq, head); variant 4: chunks a context of
-                         max_context_len tokens is cut into                   */
+                         served together), 3 bulk-copy staged without sibling groups */
+  int32_t num_warps;  /* warps working together on one (seq, head, split)   */
+  int32_t num_stages; /* pages in flight per warp (variants 2, 3)            */
+  int32_t num_splits; /* context partitions per (seq, head)                  */
 } pa_decode_tuning;
 
 /* Same operator with explicit launch shape (tuning == NULL -> automatic). */

@@ -51,7 +51,7 @@ def test_golden_reference_outputs(cid, variant):
     pt.assert_decode_close(got, pt.oracle_decode(cq), c["dtype"], f"{cid} v{variant} vs C oracle")
 
 
-@pytest.mark.parametrize("variant", [0, 1, 2, 4])
+@pytest.mark.parametrize("variant", [0, 1, 2, 3])
 @pytest.mark.parametrize("cid", cases.attention_large_case_ids())
 def test_large_goldens_config1_and_long_contexts(cid, variant):
     """BASELINE.json configs[0] as the reference test builds it (7 x 40 x 128, block 16, fp32, 1024 aliasing

@@ -236,7 +236,6 @@ struct DecodeParams {
   const int32_t* context_lens;  // [S]
   float* ws_part;             // [S][H][nsplit][D + 2]   (nsplit > 1)
   uint32_t* ws_ticket;        // [S][H], zero between calls (nsplit > 1)
-  uint32_t* ws_ctrl;          // persistent kernel: [0] next dynamic unit, [1] warps that have left; zero between calls
   int64_t q_stride;
   float scale_log2;           // scale * log2(e)
   int32_t num_heads;
@@ -294,13 +293,27 @@ paged_decode_kernel(const DecodeParams p) {
   float* red = reinterpret_cast<float*>(smem + map.red);
 
   const int first_page = split * p.pages_per_split;
+  // ---- barriers first: nothing here depends on memory, so under programmatic dependent launch this part
+  //      (and the CTA's launch itself) overlaps the tail of the preceding kernel on the stream
+  const uint32_t bars = smem_addr(smem + map.bars) + warp * p.num_stages * 8;
+  const uint32_t ring = smem_addr(smem + map.ring) + warp * p.num_stages * 2 * Gm::kPageBytes;
+  if constexpr (kStaged) {
+    if (lane == 0) {
+      for (int s = 0; s < p.num_stages; ++s) mbar_init(bars + s * 8, 1);
+      mbar_init_fence();
+    }
+  }
+  pdl_launch_dependents();
+  pdl_wait();
+  const uint64_t keep = l2_policy_evict_last();      // tables, lengths, q: re-read by every call
+  const uint64_t once = l2_policy_evict_first();     // KV pages: read exactly once per call
   // ---- stage the block-table slice (does not wait for the context length: the row is
   //      max_blocks_per_seq entries long whatever the context, so both loads fly together)
   int avail = p.max_blocks_per_seq - first_page;
   avail = avail < 0 ? 0 : (avail > p.pages_per_split ? p.pages_per_split : avail);
   {
     const int32_t* row = p.block_tables + static_cast<int64_t>(seq) * p.max_blocks_per_seq + first_page;
-    for (int i = threadIdx.x; i < avail; i += blockDim.x) tbl[i] = __ldg(row + i);
+    for (int i = threadIdx.x; i < avail; i += blockDim.x) tbl[i] = ldg_i32_hint(row + i, keep);
   }
   // sibling detection (kGroups): first page and context length of every sequence of this aligned group
   constexpr bool kGroupPath = kGroups && kStaged && T::kSize == 2 && B % 16 == 0;
@@ -310,10 +323,10 @@ paged_decode_kernel(const DecodeParams p) {
   __shared__ int s_first[kGroup];
   __shared__ int s_ctx[kGroup];
   if (grouping && threadIdx.x < nrows) {
-    s_first[threadIdx.x] = avail > 0 ? __ldg(p.block_tables + static_cast<int64_t>(r0 + threadIdx.x) * p.max_blocks_per_seq + first_page) : -1 - static_cast<int>(threadIdx.x);
-    s_ctx[threadIdx.x] = p.context_lens[r0 + threadIdx.x];
+    s_first[threadIdx.x] = avail > 0 ? ldg_i32_hint(p.block_tables + static_cast<int64_t>(r0 + threadIdx.x) * p.max_blocks_per_seq + first_page, keep) : -1 - static_cast<int>(threadIdx.x);
+    s_ctx[threadIdx.x] = ldg_i32_hint(p.context_lens + r0 + threadIdx.x, keep);
   }
-  const int ctx = p.context_lens[seq];
+  const int ctx = ldg_i32_hint(p.context_lens + seq, keep);
   // never walk past the block-table row or the split schedule, whatever context_lens says
   const int pages_true = ctx > 0 ? (ctx + B - 1) / B : 0;
   const int pages_cap = min(p.max_blocks_per_seq, p.pages_per_split * p.num_splits);
@@ -331,16 +344,6 @@ paged_decode_kernel(const DecodeParams p) {
     return;
   }
 
-  // ---- init barriers -----------------------------------------------------------
-  const uint32_t bars = smem_addr(smem + map.bars) + warp * p.num_stages * 8;
-  const uint32_t ring = smem_addr(smem + map.ring) + warp * p.num_stages * 2 * Gm::kPageBytes;
-  if constexpr (kStaged) {
-    if (lane == 0) {
-      for (int s = 0; s < p.num_stages; ++s) mbar_init(bars + s * 8, 1);
-      mbar_init_fence();
-    }
-  }
-
   // ---- q row -> registers ------------------------------------------------------
   uint4 q[Gm::kCpl];
   auto load_q = [&](int row_seq) {
@@ -353,7 +356,7 @@ paged_decode_kernel(const DecodeParams p) {
       q[cc] = make_uint4(0u, 0u, 0u, 0u);
       if (Gm::kKExact || c < Gm::kNch) {
         if (p.q_vec_ok) {
-          q[cc] = *reinterpret_cast<const uint4*>(qrow + c * 16);
+          q[cc] = ldg_v4_hint(qrow + c * 16, keep);
         } else {
           const uint16_t* h16 = reinterpret_cast<const uint16_t*>(qrow + c * 16);
           uint32_t w[4];
@@ -431,8 +434,8 @@ paged_decode_kernel(const DecodeParams p) {
           const uint32_t bar = full0 + stage * 8;
           const uint32_t dst = ring0 + stage * 2 * Gm::kPageBytes;
           mbar_expect_tx(bar, 2 * Gm::kPageBytes);
-          bulk_g2s(dst, kbase + blk * block_bytes, Gm::kPageBytes, bar);
-          bulk_g2s(dst + Gm::kPageBytes, vbase + blk * block_bytes, Gm::kPageBytes, bar);
+          bulk_g2s_hint(dst, kbase + blk * block_bytes, Gm::kPageBytes, bar, once);
+          bulk_g2s_hint(dst + Gm::kPageBytes, vbase + blk * block_bytes, Gm::kPageBytes, bar, once);
         };
         const int n1 = P > warp ? (P - warp + nwarps - 1) / nwarps : 0;            // shared pages of this warp
         if (lane == 0)
@@ -560,6 +563,9 @@ paged_decode_kernel(const DecodeParams p) {
           }
           load_q(my_seq);   // not held across phase 1: its registers carry the accumulator tiles there
         }
+        // the ring was written (xfer) and read through the generic proxy; the bulk copies of phase 2 write it
+        // through the async proxy
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
         __syncthreads();   // partials consumed: the ring carries pages again
         // Phase 2: the pages that are this sequence's own, through the warp's own S stages
         if (active) {
@@ -680,8 +686,8 @@ paged_decode_kernel(const DecodeParams p) {
       const uint32_t bar = bars + stage * 8;
       const uint32_t dst = ring + stage * 2 * Gm::kPageBytes;
       mbar_expect_tx(bar, 2 * Gm::kPageBytes);
-      bulk_g2s(dst, kbase + blk * block_bytes, Gm::kPageBytes, bar);
-      bulk_g2s(dst + Gm::kPageBytes, vbase + blk * block_bytes, Gm::kPageBytes, bar);
+      bulk_g2s_hint(dst, kbase + blk * block_bytes, Gm::kPageBytes, bar, once);
+      bulk_g2s_hint(dst + Gm::kPageBytes, vbase + blk * block_bytes, Gm::kPageBytes, bar, once);
     };
     if (lane == 0) {
       const int pre = n_my < S ? n_my : S;
@@ -806,8 +812,7 @@ struct DecodeLaunch {
   int32_t block_size;
   int32_t num_warps;
   bool staged;
-  bool persistent;            // work-queue kernel (decode_persistent.cuh): pages_per_split = pages per chunk
-  int32_t grid_ctas;          // persistent: CTAs (one per SM)
+  bool pdl;                   // launch with programmatic stream serialization (PA_DECODE_PDL=0 switches it off)
   cudaStream_t stream;
 };
 
@@ -830,10 +835,21 @@ static int launch_one(const DecodeLaunch& l) {
   if (map.total > 48 * 1024) {
     PA_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, map.total));
   }
-  const dim3 grid(l.params.num_heads, l.num_seqs, l.params.num_splits);
-  kern<<<grid, l.num_warps * kWarp, map.total, l.stream>>>(l.params);
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(l.params.num_heads, l.num_seqs, l.params.num_splits);
+  cfg.blockDim = dim3(l.num_warps * kWarp);
+  cfg.dynamicSmemBytes = map.total;
+  cfg.stream = l.stream;
+  // programmatic dependent launch: the CTAs may be placed (and set their barriers up) while the preceding
+  // kernel on the stream drains; the kernel reads no memory before griddepcontrol.wait
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = l.pdl ? 1 : 0;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  const cudaError_t e = cudaLaunchKernelEx(&cfg, kern, l.params);
   count_launch();
-  return check_cuda(cudaGetLastError(), "paged_decode_kernel launch");
+  return check_cuda(e, "paged_decode_kernel launch");
 }
 
 template <typename T, int D>

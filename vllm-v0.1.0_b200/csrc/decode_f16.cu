@@ -1,8 +1,8 @@
 // Instantiates the paged decode kernels for one element type (kept in its own
 // translation unit so the three types compile in parallel).
 #define PA_DECODE_IMPL
-#include "decode_persistent.cuh"
+#include "decode_attention.cuh"
 
 namespace pa {
-int launch_decode_f16(const DecodeLaunch& l) { return l.persistent ? launch_persistent_dtype<F16>(l) : launch_dtype<F16>(l); }
+int launch_decode_f16(const DecodeLaunch& l) { return launch_dtype<F16>(l); }
 }  // namespace pa

@@ -5,12 +5,13 @@
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <map>
 #include <mutex>
 #include <utility>
 
-#include "decode_persistent.cuh"
+#include "decode_attention.cuh"
 
 namespace pa {
 
@@ -37,8 +38,8 @@ void count_launch(uint64_t n) { g_launches.fetch_add(n, std::memory_order_relaxe
 
 // ---------------------------------------------------------------------------
 // per-(device, stream) scratch for split-context partials.
-// Layout: [control words: 256 B][tickets: items x uint32, padded to 256 B][partials: floats].
-// Control words and tickets are zeroed when the buffer is created and re-armed by the kernels; after a
+// Layout: [tickets: items x uint32, padded to 256 B][partials: floats].
+// Tickets are zeroed when the buffer is created and re-armed by the kernels; after a
 // launch that returned an error they are zeroed again before the next use (an aborted launch may have
 // left them counting).  The buffer only ever grows; growing needs a stream synchronisation, so it is
 // refused while the stream is being captured into a CUDA graph -- size it first with
@@ -47,20 +48,19 @@ void count_launch(uint64_t n) { g_launches.fetch_add(n, std::memory_order_relaxe
 struct Workspace {
   void* ptr = nullptr;
   size_t bytes = 0;
-  size_t ticket_bytes = 0;   // control words included
+  size_t ticket_bytes = 0;
   bool dirty = false;
 };
-constexpr size_t kCtrlBytes = 256;
 static std::mutex g_ws_mu;
 static std::map<std::pair<int, cudaStream_t>, Workspace> g_ws;
 
-static int get_workspace(cudaStream_t stream, size_t ticket_bytes, size_t part_bytes, uint32_t** ctrl,
-                         uint32_t** tickets, float** parts) {
+static int get_workspace(cudaStream_t stream, size_t ticket_bytes, size_t part_bytes, uint32_t** tickets,
+                         float** parts) {
   int dev = 0;
   PA_CUDA_TRY(cudaGetDevice(&dev));
   std::lock_guard<std::mutex> lock(g_ws_mu);
   Workspace& w = g_ws[std::make_pair(dev, stream)];
-  ticket_bytes = kCtrlBytes + (ticket_bytes + 255) / 256 * 256;
+  ticket_bytes = (ticket_bytes + 255) / 256 * 256;
   part_bytes = (part_bytes + 255) / 256 * 256;
   if (w.ticket_bytes < ticket_bytes || w.bytes - w.ticket_bytes < part_bytes) {
     cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
@@ -74,7 +74,7 @@ static int get_workspace(cudaStream_t stream, size_t ticket_bytes, size_t part_b
       PA_CUDA_TRY(cudaFree(w.ptr));
       w = Workspace();
     }
-    const size_t tb = kCtrlBytes + (ticket_bytes - kCtrlBytes) * 2;   // head-room: item count may grow
+    const size_t tb = ticket_bytes * 2;            // head-room: item count may grow
     const size_t total = tb + part_bytes * 2;
     PA_CUDA_TRY(cudaMalloc(&w.ptr, total));
     w.bytes = total;
@@ -85,8 +85,7 @@ static int get_workspace(cudaStream_t stream, size_t ticket_bytes, size_t part_b
     PA_CUDA_TRY(cudaMemsetAsync(w.ptr, 0, w.ticket_bytes, stream));
     w.dirty = false;
   }
-  *ctrl = static_cast<uint32_t*>(w.ptr);
-  *tickets = reinterpret_cast<uint32_t*>(static_cast<char*>(w.ptr) + kCtrlBytes);
+  *tickets = static_cast<uint32_t*>(w.ptr);
   *parts = reinterpret_cast<float*>(static_cast<char*>(w.ptr) + w.ticket_bytes);
   return PA_OK;
 }
@@ -145,73 +144,14 @@ int decode_smem_bytes(int dtype, int head_size, int block_size, int pages_per_sp
 }
 
 
-// bytes of dynamic shared memory of the persistent kernel (same formula as PersistMap)
-int persistent_smem_bytes(int dtype, int head_size, int block_size, int num_seqs, int warps, int stages) {
-  const int es = dtype_size(dtype);
-  const int page = head_size * block_size * es;
-  const int pbuf = ((2 * block_size * es + 15) / 16) * 16;
-  int o = ((num_seqs * 4 + 15) / 16) * 16;
-  o += (((num_seqs + 1) * 4 + 15) / 16) * 16;
-  o += warps * (2 * head_size * es + pbuf);
-  o += warps * stages * 8;
-  o = ((o + 127) / 128) * 128;
-  o += warps * stages * 2 * page;
-  return o;
-}
-
-// Launch shape of the persistent work-queue kernel (variant 4): one CTA per SM of `num_warps` independent
-// warps, `num_stages` (K page + V page) stages per warp, contexts cut into `num_splits` chunks at most
-// (pages per chunk through the pointer).  Sizing rules (sweeps in profiles/r2_sweep_persistent.json):
-// ring bytes per SM near the shared-memory limit; chunks so that every warp sees >= ~8 units, never below
-// 64 KiB of KV per unit (each unit costs a partial + a ticket) and never above 512 KiB (the launch's tail
-// is one unit per warp at one warp's own ring bandwidth).
-static int make_persistent_plan(int num_seqs, int num_heads, int head_size, int block_size,
-                                int max_blocks_per_seq, int max_context_len, int dtype, pa_decode_tuning* t,
-                                int* pages_per_chunk) {
-  if (num_seqs > kPersistMaxSeqs)
-    return set_error(PA_ERR_INVALID_ARGUMENT, "variant 4 holds the batch plan in shared memory: %d sequences > %d",
-                     num_seqs, kPersistMaxSeqs);
-  const int es = dtype_size(dtype);
-  const int stage = 2 * head_size * block_size * es;
-  int max_pages = max_context_len > 0 ? (max_context_len + block_size - 1) / block_size : 1;
-  if (max_blocks_per_seq > 0 && max_pages > max_blocks_per_seq) max_pages = max_blocks_per_seq;
-  const int budget = kMaxSmem - persistent_smem_bytes(dtype, head_size, block_size, num_seqs, 0, 0);
-  const int misc = 2 * head_size * es + ((2 * block_size * es + 15) / 16) * 16;
-  if (t->num_stages <= 0) {
-    t->num_stages = 2;
-    if (t->num_warps <= 0) {
-      int w = budget / (2 * (stage + 8) + misc);
-      t->num_warps = w > 16 ? 16 : (w < 1 ? 1 : w);
-    }
-    int s = (budget / t->num_warps - misc) / (stage + 8);      // spend what is left on ring depth
-    t->num_stages = s > 8 ? 8 : (s < 2 ? 2 : s);
-  } else if (t->num_warps <= 0) {
-    int w = budget / (t->num_stages * (stage + 8) + misc);
-    t->num_warps = w > 16 ? 16 : (w < 1 ? 1 : w);
-  }
-  if (t->num_warps > 16) t->num_warps = 16;
-  if (t->num_stages > 32) t->num_stages = 32;
-  if (persistent_smem_bytes(dtype, head_size, block_size, num_seqs, t->num_warps, t->num_stages) > kMaxSmem)
-    return set_error(PA_ERR_INVALID_ARGUMENT, "launch shape does not fit shared memory (warps %d, stages %d)",
-                     t->num_warps, t->num_stages);
-  if (t->num_splits <= 0) {
-    const double total = static_cast<double>(num_seqs) * num_heads * max_pages * stage;
-    const double workers = static_cast<double>(sm_count()) * t->num_warps;
-    double unit = total / (workers * 8.0);
-    if (unit < 64.0 * 1024) unit = 64.0 * 1024;
-    if (unit > 512.0 * 1024) unit = 512.0 * 1024;
-    int c = static_cast<int>(unit / stage);
-    if (c < 1) c = 1;
-    t->num_splits = (max_pages + c - 1) / c;
-  }
-  if (t->num_splits > max_pages) t->num_splits = max_pages;
-  if (t->num_splits < 1) t->num_splits = 1;
-  const int c = (max_pages + t->num_splits - 1) / t->num_splits;
-  t->num_splits = (max_pages + c - 1) / c;
-  *pages_per_chunk = c;
-  if (static_cast<int64_t>(num_seqs) * num_heads * t->num_splits >= (int64_t{1} << 31) - 4 * 148 * 16)
-    return set_error(PA_ERR_INVALID_ARGUMENT, "too many work units");
-  return PA_OK;
+// CTAs of this launch shape that fit one SM (shared memory, threads)
+static int resident_ctas(int dtype, int head_size, int block_size, int warps, int stages, bool staged) {
+  const int smem1 = decode_smem_bytes(dtype, head_size, block_size, 64, warps, stages, staged);
+  int resident = kMaxSmem / (smem1 + 1024);
+  const int by_threads = 2048 / (warps * kWarp);
+  if (resident > by_threads) resident = by_threads;
+  if (resident > 32) resident = 32;
+  return resident < 1 ? 1 : resident;
 }
 
 constexpr int kMaxPagesPerSplit = 8192;  // block-table slice kept in shared memory (32 KiB)
@@ -233,6 +173,7 @@ static int make_plan(int num_seqs, int num_heads, int head_size, int block_size,
 
   if (t->variant <= 0) t->variant = 2;
   const bool staged = t->variant >= 2;
+  const bool auto_warps = t->num_warps <= 0;
   if (t->num_warps <= 0) {
     t->num_warps = max_pages <= 4 ? 1 : (max_pages <= 8 ? 2 : 4);
     while (staged && t->num_warps > 1 && t->num_warps * 2 * stage > 160 * 1024) t->num_warps >>= 1;
@@ -241,14 +182,20 @@ static int make_plan(int num_seqs, int num_heads, int head_size, int block_size,
   if (t->num_stages <= 0) t->num_stages = 2;
   if (!staged) t->num_stages = 1;
   if (t->num_stages > 32) t->num_stages = 32;
+  // Just over one wave of short items (444 < items <= 1.25 x 444 at 4 warps, <= 64 pages): the second wave
+  // would run nearly empty behind a full first one and pay a second prologue; CTAs of two warps fit twice as
+  // many per SM, so the launch becomes a single wave with every page in flight from the start (measured,
+  // profiles/r1_short_ctx_vs_reference_kernel.json S16_L512: 28.8 -> 25.0 us; profiles/r2_wave_probe_h5.json
+  // shows the step at the first wave boundary, +6..9 us, and none at the later ones).
+  if (auto_warps && staged && t->num_warps == 4 && max_pages <= 64) {
+    const int64_t items = static_cast<int64_t>(num_seqs) * num_heads;
+    const int64_t slots4 = static_cast<int64_t>(sm_count()) *
+                           resident_ctas(dtype, head_size, block_size, 4, t->num_stages, staged);
+    if (items > slots4 && items * 4 <= slots4 * 5) t->num_warps = 2;
+  }
 
   if (t->num_splits <= 0) {
-    const int smem1 = decode_smem_bytes(dtype, head_size, block_size, 64, t->num_warps, t->num_stages, staged);
-    int resident = kMaxSmem / (smem1 + 1024);
-    const int by_threads = 2048 / (t->num_warps * kWarp);
-    if (resident > by_threads) resident = by_threads;
-    if (resident > 32) resident = 32;
-    if (resident < 1) resident = 1;
+    const int resident = resident_ctas(dtype, head_size, block_size, t->num_warps, t->num_stages, staged);
     const int64_t items = static_cast<int64_t>(num_seqs) * num_heads;
     const int64_t slots = static_cast<int64_t>(sm_count()) * resident;
     int64_t ns = items > 0 ? slots / items : 1;                  // fill the slots once, no more
@@ -310,12 +257,9 @@ static int decode(void* out, const void* query, const void* key_cache, const voi
 
   pa_decode_tuning t = {0, 0, 0, 0};
   if (tuning) t = *tuning;
-  if (t.variant < 0 || t.variant > 4) return set_error(PA_ERR_INVALID_ARGUMENT, "invalid variant %d", t.variant);
-  const bool persistent = t.variant == 4;
+  if (t.variant < 0 || t.variant > 3) return set_error(PA_ERR_INVALID_ARGUMENT, "invalid variant %d", t.variant);
   int pps = 0;
-  rc = persistent ? make_persistent_plan(num_seqs, num_heads, head_size, block_size, max_num_blocks_per_seq,
-                                         max_context_len, dtype, &t, &pps)
-                  : make_plan(num_seqs, num_heads, head_size, block_size, max_context_len, dtype, &t, &pps);
+  rc = make_plan(num_seqs, num_heads, head_size, block_size, max_context_len, dtype, &t, &pps);
   if (rc != PA_OK) return rc;
 
   DecodeLaunch l;
@@ -332,20 +276,19 @@ static int decode(void* out, const void* query, const void* key_cache, const voi
   p.num_stages = t.num_stages;
   p.q_vec_ok = (reinterpret_cast<uintptr_t>(query) % 16 == 0) && ((q_stride * es) % 16 == 0);
   p.num_seqs = num_seqs;
-  p.group_rows = persistent ? 1 :
-                 group_rows_for(t.variant >= 2, t.variant, t.num_warps, num_seqs, dtype, block_size,
+  p.group_rows = group_rows_for(t.variant >= 2, t.variant, t.num_warps, num_seqs, dtype, block_size,
                                 decode_smem_bytes(dtype, head_size, block_size, pps, t.num_warps, t.num_stages, t.variant >= 2));
-  if (t.num_splits > 1 || persistent) {
+  if (t.num_splits > 1) {
     const size_t items = static_cast<size_t>(num_seqs) * num_heads;
-    const size_t parts = t.num_splits > 1 ? items * t.num_splits * (head_size + 2) * sizeof(float) : 0;
-    rc = get_workspace(stream, t.num_splits > 1 ? items * sizeof(uint32_t) : 0, parts, &p.ws_ctrl, &p.ws_ticket,
-                       &p.ws_part);
+    rc = get_workspace(stream, items * sizeof(uint32_t), items * t.num_splits * (head_size + 2) * sizeof(float),
+                       &p.ws_ticket, &p.ws_part);
     if (rc != PA_OK) return rc;
   }
   if (reserve_only) return PA_OK;
   l.num_seqs = num_seqs; l.head_size = head_size; l.block_size = block_size;
-  l.num_warps = t.num_warps; l.staged = (t.variant >= 2); l.persistent = persistent; l.grid_ctas = sm_count();
-  l.stream = stream;
+  l.num_warps = t.num_warps; l.staged = (t.variant >= 2); l.stream = stream;
+  static const bool pdl = [] { const char* e = getenv("PA_DECODE_PDL"); return !(e && e[0] == '0'); }();
+  l.pdl = pdl;
   switch (dtype) {
     case PA_F16:  rc = launch_decode_f16(l); break;
     case PA_BF16: rc = launch_decode_bf16(l); break;
@@ -414,8 +357,6 @@ int pa_decode_attention_plan(int32_t num_seqs, int32_t num_heads, int32_t head_s
   int rc = pa::check_shape(head_size, block_size, dtype);
   if (rc != PA_OK) return rc;
   int pps = 0;
-  if (plan_out->variant == 4)
-    return pa::make_persistent_plan(num_seqs, num_heads, head_size, block_size, 0, max_context_len, dtype, plan_out, &pps);
   return pa::make_plan(num_seqs, num_heads, head_size, block_size, max_context_len, dtype, plan_out, &pps);
 }
 

@@ -235,6 +235,43 @@ __device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t
       :: "r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
 }
 
+// L2 residency: every KV byte is read exactly once per call (evict_first), the block tables, context lengths
+// and q rows are read by every call and sit on the critical path of each CTA's prologue (evict_last).
+__device__ __forceinline__ uint64_t l2_policy_evict_first() {
+  uint64_t pol;
+  asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+  return pol;
+}
+__device__ __forceinline__ uint64_t l2_policy_evict_last() {
+  uint64_t pol;
+  asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol));
+  return pol;
+}
+__device__ __forceinline__ void bulk_g2s_hint(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar,
+                                              uint64_t policy) {
+  asm volatile(
+      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;"
+      :: "r"(dst), "l"(src), "r"(bytes), "r"(bar), "l"(policy) : "memory");
+}
+__device__ __forceinline__ int32_t ldg_i32_hint(const int32_t* p, uint64_t policy) {
+  int32_t v;
+  asm volatile("ld.global.nc.L2::cache_hint.b32 %0, [%1], %2;" : "=r"(v) : "l"(p), "l"(policy));
+  return v;
+}
+__device__ __forceinline__ uint4 ldg_v4_hint(const void* p, uint64_t policy) {
+  uint4 r;
+  asm volatile("ld.global.nc.L2::cache_hint.v4.u32 {%0, %1, %2, %3}, [%4], %5;"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p), "l"(policy));
+  return r;
+}
+
+// Programmatic dependent launch.  pdl_wait(): everything the preceding kernel on the stream wrote is visible
+// after it (a no-op for a launch without the attribute).  pdl_launch_dependents(): the next kernel on the
+// stream, if it was launched with the attribute, may start its CTAs as resources free up; it must pdl_wait()
+// before it reads anything this kernel writes.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
 #endif  // __CUDACC__
 
 }  // namespace pa
