@@ -10,13 +10,22 @@ BASELINE.json configs[2], the one the metric's "1/2/4/8 B200" refers to: LLaMA-1
 (40/N per GPU, replicated block tables, no collective on the path) -> "scaling": "strong".
 At N=1 the line also carries configs[1] (LLaMA-7B, fp16) under "also".
 
-Prints ONE JSON line (rank 0).  See DESIGN.md "Measurement" for how each field is obtained.
+Besides the headline numbers the ONE JSON line (rank 0) carries, all measured in this run:
+  check                 rank 0's output rows against the CPU oracle (a sample of sequences, all local heads)
+  e2e                   host-buffer round trip per step, serial and pipelined
+  gpu_reference_kernel  the reference's own CUDA kernel (oracle/_ref, built unmodified for sm_100) on the same
+                        tensors, timed in a SUBPROCESS so that this process never maps it
+  also (N = 1)          BASELINE.json configs[1] and configs[4] decode shapes, the configs[3] cache movers, the
+                        prompt kernel next to the library kernel
+  allreduce (N > 1)     the row-parallel all-reduce that follows attention: multimem / peer / NCCL
+See DESIGN.md "Measurement" for how each field is obtained.
 """
 from __future__ import annotations
 
 import argparse
 import json
 import os
+import subprocess
 import sys
 import threading
 import time
@@ -230,6 +239,79 @@ def run_e2e_steps(p, steps, warmup, barrier):
     return e0.elapsed_time(e1), (t0, t1), h2d, d2h
 
 
+def run_e2e_pipelined(p, steps, warmup, barrier):
+    """The same host-buffer round trip with the fixed copy latencies overlapped: two staging arenas and two
+    output buffers; step i's inputs go up on an upload stream while step i-1's kernel runs, step i's result
+    comes down on a download stream while step i+1 runs.  Contract: the result of step i is in host memory
+    before step i+2 is issued (the host blocks on it then), and every step's bytes still cross PCIe inside
+    the timed region."""
+    import torch
+    from vllm_b200 import attention_ops
+    dev = p["q"].device
+    q_src, t_src, l_src = p["q"].contiguous().cpu(), p["tables_host"], p["lens_host"]
+    sizes = [t.numel() * t.element_size() for t in (q_src, t_src, l_src)]
+    offs = [0, (sizes[0] + 255) // 256 * 256]
+    offs.append(offs[1] + (sizes[1] + 255) // 256 * 256)
+    total = offs[2] + sizes[2]
+
+    def view(arena, i, like):
+        return arena[offs[i]:offs[i] + sizes[i]].view(like.dtype).view(like.shape)
+    slots = []
+    for _ in range(2):
+        ah = torch.empty(total, dtype=torch.uint8).pin_memory()
+        ad = torch.empty(total, dtype=torch.uint8, device=dev)
+        for i, src in enumerate((q_src, t_src, l_src)):
+            view(ah, i, src).copy_(src)
+        slots.append(dict(ah=ah, ad=ad, q=view(ad, 0, q_src), t=view(ad, 1, t_src), l=view(ad, 2, l_src),
+                          out_d=torch.empty(q_src.shape, dtype=p["dtype"], device=dev),
+                          out_h=torch.empty(q_src.shape, dtype=p["dtype"]).pin_memory(),
+                          up=torch.cuda.Event(), done=torch.cuda.Event(), down=torch.cuda.Event(), used=False))
+    main_s = torch.cuda.current_stream()
+    up_s, down_s = torch.cuda.Stream(device=dev), torch.cuda.Stream(device=dev)
+
+    def step(i):
+        s = slots[i & 1]
+        if s["used"]:
+            s["down"].synchronize()                    # the host holds step i-2's result before its buffers are reused
+        with torch.cuda.stream(up_s):
+            if s["used"]:
+                up_s.wait_event(s["done"])             # step i-2's kernel has read this arena
+            s["ad"].copy_(s["ah"], non_blocking=True)
+            s["up"].record(up_s)
+        main_s.wait_event(s["up"])
+        attention_ops.single_query_cached_kv_attention(s["out_d"], s["q"], p["kc"], p["vc"], p["scale"], s["t"], s["l"],
+                                                       p["B"], p["L"])
+        s["done"].record(main_s)
+        with torch.cuda.stream(down_s):
+            down_s.wait_event(s["done"])
+            s["out_h"].copy_(s["out_d"], non_blocking=True)
+            s["down"].record(down_s)
+        s["used"] = True
+
+    def drain():
+        for s in slots:
+            if s["used"]:
+                main_s.wait_event(s["down"])
+                s["down"].synchronize()
+
+    for i in range(warmup):
+        step(i)
+    drain()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    e0.record()
+    for i in range(steps):
+        step(warmup + i)
+    drain()                                            # the last results are on the host inside the timed region
+    e1.record()
+    torch.cuda.synchronize()
+    t1 = time.perf_counter()
+    barrier()
+    return e0.elapsed_time(e1), (t0, t1)
+
+
 # ---------------------------------------------------------------------------
 # CPU side: the reference's PyTorch path (restated in oracle/paged_oracle.py) on host cores
 # ---------------------------------------------------------------------------
@@ -277,6 +359,33 @@ def time_cpu_reference(wl, nseq, steps=1, warmup=0):
     return (time.perf_counter() - t0) / steps
 
 
+def time_cpu_config1():
+    """BASELINE.json configs[0] as the reference test builds it (tests/kernels/test_attention.py:159-224,270-287):
+    7 sequences x 40 heads x 128, block 16, fp32, 1024 blocks, context lengths and aliasing block tables from
+    random.seed(0); one pass of the PyTorch loop reference on all host threads.  Values are uniform like the
+    test's (their bits do not matter for the timing)."""
+    import random
+    import torch
+    from oracle import paged_oracle
+    threads = use_all_host_threads()
+    rnd = random.Random(0)
+    S, H, D, B, NB = 7, 40, 128, 16, 1024
+    ctx = [rnd.randint(1, 4096) for _ in range(S)]
+    mb = (max(ctx) + B - 1) // B
+    tables = torch.tensor([[rnd.randint(0, NB - 1) for _ in range(mb)] for _ in range(S)], dtype=torch.int32)
+    g = torch.Generator().manual_seed(0)
+    q = torch.rand((S, H, D), generator=g) * 2e-3 - 1e-3
+    kc = torch.rand((NB, H, D // 4, B, 4), generator=g) * 2e-3 - 1e-3
+    vc = torch.rand((NB, H, D, B), generator=g) * 2e-3 - 1e-3
+    out = torch.empty_like(q)
+    lens = torch.tensor(ctx, dtype=torch.int32)
+    t0 = time.perf_counter()
+    paged_oracle.decode_attention_loop(out, q, kc, vc, tables, lens)
+    sec = time.perf_counter() - t0
+    return {"seconds": sec, "seqs_per_s": S / sec, "cores": threads,
+            "shape": "7 seqs x 40 heads x 128, block 16, fp32, 1024 blocks, contexts <= 4096 (random.seed(0))"}
+
+
 def cpu_sample_size(wl, budget_s, cap):
     """Sequences per CPU pass so that one pass takes about `budget_s` (calibrated on one sequence)."""
     one = time_cpu_reference(wl, 1)
@@ -316,14 +425,264 @@ def run_reference(args, wl):
     print(json.dumps(line), flush=True)
 
 
-def traffic_from_profiles(workload):
-    """dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed ncu --set full
-    capture of this workload's kernel (profiles/roofline_traffic.json), or None."""
+def traffic_from_profiles(workload, heads_local):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed ncu --set full capture of this
+    workload's decode kernel at this many heads per GPU (profiles/roofline_traffic.json), or None when no
+    capture of exactly that shape is on file."""
     try:
         with open(os.path.join(ROOT, "profiles", "roofline_traffic.json")) as f:
-            return json.load(f).get(workload, {}).get("dram_bytes_per_launch")
+            return json.load(f).get(workload, {}).get(str(heads_local), {}).get("dram_bytes_per_launch")
     except Exception:
         return None
+
+
+# ---------------------------------------------------------------------------
+# checker: rank 0's output against the CPU oracle on a sample of sequences (outside every timed region)
+# ---------------------------------------------------------------------------
+def oracle_row_check(p, out, nrows=3):
+    """Pulls the pages of `nrows` sequences back from the GPU cache, runs the C oracle (double precision) on
+    them for all local heads and compares with the kernel's rows at the north-star tolerance of the dtype."""
+    import torch
+    from oracle import c_oracle
+    S = p["q"].shape[0]
+    rows = sorted(set([0, S // 2, S - 1][:nrows]))
+    idx = torch.tensor(rows, dtype=torch.long)
+    tables, lens = p["tables_host"][idx], p["lens_host"][idx]
+    used = torch.unique(tables)
+    remap = torch.zeros(int(used.max()) + 1, dtype=torch.int32)
+    remap[used.long()] = torch.arange(len(used), dtype=torch.int32)
+    dev = p["q"].device
+    kc = p["kc"][used.long().to(dev)].cpu()
+    vc = p["vc"][used.long().to(dev)].cpu()
+    q = p["q"][idx.to(dev)].cpu().contiguous()
+    want = torch.empty(q.shape, dtype=q.dtype)
+    c_oracle.decode_attention(want, q, kc, vc, p["scale"], remap[tables.long()].contiguous(), lens.contiguous())
+    got = out[idx.to(dev)].float().cpu()
+    w = want.float()
+    tol = {torch.float16: 1e-3, torch.bfloat16: 1e-2, torch.float32: 1e-4}[p["dtype"]]
+    err = (got - w).abs()
+    bound = tol * float(w.abs().max()) + tol * w.abs()
+    return {"rows": rows, "heads": int(q.shape[1]), "max_abs_err": float(err.max()), "max_abs_want": float(w.abs().max()),
+            "tolerance": tol, "ok": bool((err <= bound).all() and torch.isfinite(got).all()),
+            "checker": "oracle/paged_oracle.c (double precision) on the pages of these sequences"}
+
+
+# ---------------------------------------------------------------------------
+# the reference's own CUDA kernel on the same tensors (subprocess: this process never maps oracle/_ref)
+# ---------------------------------------------------------------------------
+def ref_kernel_leg(workload, heads_local, device_index, iters=10):
+    """Child process: loads oracle/_ref/ref_attention_ops.so (the reference's csrc/attention compiled unmodified
+    for sm_100 by oracle/build_ref.py) and times it next to ours on the same seeded tensors."""
+    import importlib.util
+    import torch
+    so = os.path.join(ROOT, "oracle", "_ref", "ref_attention_ops.so")
+    if not os.path.exists(so):
+        print(json.dumps({"unavailable": "oracle/_ref/ref_attention_ops.so is not built (oracle/build_ref.py needs /root/reference)"}))
+        return
+    torch.cuda.set_device(device_index)
+    dev = torch.device("cuda", device_index)
+    wl = WORKLOADS[workload]
+    p = make_problem(wl, heads_local, dev)
+    if p["kc"].numel() >= 2 ** 31:
+        print(json.dumps({"unavailable": "the reference kernel indexes with 32-bit int (attention_kernels.cu:157,243): "
+                                         f"{p['kc'].numel()} cache elements overflow it"}))
+        return
+    spec = importlib.util.spec_from_file_location("ref_attention_ops", so)
+    ref = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(ref)
+    from vllm_b200 import attention_ops
+    out_a = torch.empty(p["q"].shape, dtype=p["dtype"], device=dev)
+    out_b = torch.empty_like(out_a)
+
+    def timed(fn):
+        for _ in range(3):
+            fn()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize()
+        e0.record()
+        for _ in range(iters):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / iters
+    ms_ours = timed(lambda: attention_ops.single_query_cached_kv_attention(out_a, p["q"], p["kc"], p["vc"], p["scale"],
+                                                                          p["tables"], p["lens"], p["B"], p["L"]))
+    ms_ref = timed(lambda: ref.single_query_cached_kv_attention(out_b, p["q"], p["kc"], p["vc"], p["scale"], p["tables"],
+                                                                p["lens"], p["B"], p["L"]))
+    nbytes = algorithmic_bytes(wl["seqs"], heads_local, wl["head_size"], wl["block_size"], wl["ctx"], p["kc"].element_size())
+    diff = float((out_a.float() - out_b.float()).abs().max() / out_b.float().abs().max())
+    print(json.dumps({"workload": workload, "heads_per_gpu": heads_local, "ms": ms_ref, "gbs": nbytes / ms_ref / 1e6,
+                      "ours_ms": ms_ours, "ours_gbs": nbytes / ms_ours / 1e6, "speedup": ms_ref / ms_ours,
+                      "max_rel_diff": diff,
+                      "what": "reference csrc/attention/attention_kernels.cu compiled unmodified for sm_100, same tensors, "
+                              f"CUDA events over {iters} back-to-back calls each"}))
+
+
+def gpu_reference_kernel(workload, heads_local, device_index):
+    try:
+        env = {k: v for k, v in os.environ.items()
+               if k not in ("RANK", "LOCAL_RANK", "WORLD_SIZE", "MASTER_ADDR", "MASTER_PORT", "OMP_NUM_THREADS")}
+        r = subprocess.run([sys.executable, os.path.abspath(__file__), "--leg", "ref-kernel", "--workload", workload,
+                            "--heads-local", str(heads_local), "--device-index", str(device_index)],
+                           capture_output=True, text=True, timeout=300, env=env)
+        lines = [l for l in r.stdout.splitlines() if l.startswith("{")]
+        if r.returncode != 0 or not lines:
+            return {"unavailable": f"child exited {r.returncode}: {r.stderr.strip()[-300:]}"}
+        return json.loads(lines[-1])
+    except Exception as e:
+        return {"unavailable": repr(e)[:300]}
+
+
+# ---------------------------------------------------------------------------
+# N = 1 extras: configs[4] decode shapes, configs[3] cache movers, the prompt kernel
+# ---------------------------------------------------------------------------
+def _time_events(fn, iters, warm=3):
+    import torch
+    for _ in range(warm):
+        fn()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    e0.record()
+    for _ in range(iters):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / iters
+
+
+def decode_block(name, dev, steps, warmup, peak):
+    """One more decode workload on this GPU: device-timed value, roofline against the same measured peak, e2e."""
+    import torch
+    wl = WORKLOADS[name]
+    p = make_problem(wl, wl["heads"], dev)
+    nobar = lambda: None
+    ms, _, _, out = run_kernel_steps(p, steps, warmup, nobar)
+    chk = oracle_row_check(p, out, nrows=2)
+    mse, _, _, _ = run_e2e_steps(p, steps, warmup, nobar)
+    esize = p["kc"].element_size()
+    b = algorithmic_bytes(wl["seqs"], wl["heads"], wl["head_size"], wl["block_size"], wl["ctx"], esize)
+    t = ms / steps / 1e3
+    blk = {"config": workload_config(name, wl, 1, wl["heads"]), "dtype": wl["dtype"],
+           "value": wl["seqs"] / t, "unit": "seqs/s", "ms_per_step": t * 1e3, "hbm_gbs": b / t / 1e9,
+           "roofline": {"bound": "hbm", "achieved": b / t / 1e9, "peak": peak, "unit": "GB/s", "frac": b / t / 1e9 / peak,
+                        "traffic": traffic_from_profiles(name, wl["heads"]), "algorithmic_bytes_per_launch": b},
+           "frac_of_8tbs": b / t / 1e9 / NOMINAL_HBM_GBS, "e2e_value": wl["seqs"] / (mse / steps / 1e3), "check": chk}
+    del p, out
+    torch.cuda.empty_cache()
+    return blk
+
+
+def movers_block(dev, peak):
+    """BASELINE.json configs[3] (OPT-13B, 40 layers x 40 heads x 128, block 16, fp16): copy_blocks for one
+    decode step of 64 groups forking 3 siblings each (192 pairs, every layer), swap_blocks of 512 scattered
+    blocks each way, reshape_and_cache of a decode step (256 tokens) and of a prompt batch (2560 tokens).
+    Algorithmic bytes per SURVEY.md section 8(d).  Every result is checked bit for bit against torch indexing."""
+    import torch
+    from vllm_b200 import cache_ops
+    layers, H, D, B, NB = 40, 40, 128, 16, 1024
+    g = torch.Generator(device=dev).manual_seed(7)
+    kcs = [torch.empty((NB, H, D // 8, B, 8), dtype=torch.float16, device=dev).normal_(generator=g) for _ in range(layers)]
+    vcs = [torch.empty((NB, H, D, B), dtype=torch.float16, device=dev).normal_(generator=g) for _ in range(layers)]
+    blk_bytes = H * D * B * 2
+    res = {"config": {"workload": "opt13b_cache_movers", "note": "BASELINE.json configs[3]: OPT-13B parallel sampling n=4 / "
+                      "beam 4 cache traffic", "layers": layers, "num_heads": H, "head_size": D, "block_size": B,
+                      "num_blocks": NB, "kv_dtype": "fp16", "block_bytes": blk_bytes}}
+    # copy_blocks
+    mapping = {}
+    for i in range(192):
+        mapping.setdefault(i // 3, []).append(512 + i)
+    ms = _time_events(lambda: cache_ops.copy_blocks(kcs, vcs, mapping), iters=20)
+    ok = all(torch.equal(kcs[l][512 + i], kcs[l][i // 3]) and torch.equal(vcs[l][512 + i], vcs[l][i // 3])
+             for l in (0, layers - 1) for i in (0, 95, 191))
+    nbytes = 2 * 192 * layers * 2 * blk_bytes          # read + write, K and V
+    res["copy_blocks"] = {"pairs": 192, "layers": layers, "ms": ms, "bit_exact": ok,
+                          "roofline": {"bound": "hbm", "achieved": nbytes / ms / 1e6, "peak": peak, "unit": "GB/s",
+                                       "frac": nbytes / ms / 1e6 / peak, "traffic": None, "algorithmic_bytes_per_launch": nbytes,
+                                       "note": "read + write bytes; sources are re-read from L2 by their 3 destinations"}}
+    # reshape_and_cache
+    for N, label in ((256, "decode_step"), (2560, "prompt_batch")):
+        qkv = torch.empty((N, 3, H, D), dtype=torch.float16, device=dev).normal_(generator=g)
+        if N <= 256:     # decode step: every token is the newest token of its own sequence -> its own block
+            slots = (torch.randperm(NB, device=dev)[:N] * B + torch.randint(0, B, (N,), device=dev)).to(torch.int32)
+        else:            # prompts of 512 tokens fill consecutive slots of scattered block runs
+            starts = torch.randperm(NB // 32, device=dev)[:N // 512] * 32 * B
+            slots = (starts[:, None] + torch.arange(512, device=dev)[None, :]).flatten().to(torch.int32)
+        kc, vc = kcs[0], vcs[0]
+        ms = _time_events(lambda: cache_ops.reshape_and_cache(qkv[:, 1], qkv[:, 2], kc, vc, slots), iters=50)
+        sl = slots.long()
+        got_k = kc[sl // B, :, :, sl % B, :].reshape(N, H, D)        # [N, H, D/x, x] -> [N, H, D]
+        got_v = vc[sl // B, :, :, sl % B]
+        ok = bool(torch.equal(got_k, qkv[:, 1]) and torch.equal(got_v, qkv[:, 2]))
+        nbytes = N * H * D * 2 * 2 * 2                     # K and V rows read + written
+        res[f"reshape_and_cache_{label}"] = {
+            "tokens": N, "ms": ms, "bit_exact": ok,
+            "roofline": {"bound": "hbm", "achieved": nbytes / ms / 1e6, "peak": peak, "unit": "GB/s",
+                         "frac": nbytes / ms / 1e6 / peak, "traffic": None, "algorithmic_bytes_per_launch": nbytes,
+                         "note": "a launch this small is bound by launch + DRAM latency, not bandwidth"}}
+    # swap_blocks
+    cpu = torch.empty((NB, H, D, B), dtype=torch.float16).pin_memory()
+    gp = torch.Generator().manual_seed(3)
+    src_ids, dst_ids = torch.randperm(NB, generator=gp)[:512].tolist(), torch.randperm(NB, generator=gp)[:512].tolist()
+    mp = {int(a): int(b) for a, b in zip(src_ids, dst_ids)}
+    pcie = 63.0          # GB/s, PCIe Gen5 x16 per direction (nominal; no measured figure in MEASURED_PEAKS.json)
+    for direction, (src, dst) in (("gpu_to_cpu", (vcs[0], cpu)), ("cpu_to_gpu", (cpu, vcs[1]))):
+        ms = _time_events(lambda: cache_ops.swap_blocks(src, dst, mp), iters=5, warm=2)
+        torch.cuda.synchronize()
+        probe = [(src_ids[i], dst_ids[i]) for i in (0, 255, 511)]
+        ok = all(torch.equal(dst[d].cpu(), src[s_].cpu()) for s_, d in probe)
+        nbytes = 512 * blk_bytes
+        res[f"swap_blocks_{direction}"] = {
+            "blocks": 512, "ms": ms, "bit_exact": ok,
+            "roofline": {"bound": "pcie", "achieved": nbytes / ms / 1e6, "peak": pcie, "unit": "GB/s",
+                         "frac": nbytes / ms / 1e6 / pcie, "traffic": None, "algorithmic_bytes_per_launch": nbytes,
+                         "peak_source": "nominal PCIe Gen5 x16, one direction"}}
+    del kcs, vcs, cpu
+    torch.cuda.empty_cache()
+    return res
+
+
+def prefill_block(dev):
+    """The prompt kernel (pa_prefill_attention, tcgen05) next to the library kernel on this GPU (torch SDPA ->
+    cuDNN) on the same tensors; roofline against the measured bf16 tensor peak."""
+    import torch
+    import torch.nn.functional as F
+    from vllm_b200 import attention_ops
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            pk = json.load(f)
+        peak, peak_src = float(pk["bf16_tflops"]), "measured (MEASURED_PEAKS.json bf16_tflops, cuBLAS burst)"
+    except Exception:
+        peak, peak_src = 1590.0, "fallback (B200_PROFILING.md 1.59 PFLOP/s)"
+    rows = []
+    for name, h, d, lens in (("llama13b_5x512", 40, 128, [512] * 5), ("llama13b_8x2048", 40, 128, [2048] * 8)):
+        n = sum(lens)
+        g = torch.Generator(device=dev).manual_seed(0)
+        qkv = torch.empty((n, 3, h, d), dtype=torch.bfloat16, device=dev).normal_(generator=g)
+        q, k, v = qkv[:, 0], qkv[:, 1], qkv[:, 2]
+        out = torch.empty((n, h, d), dtype=torch.bfloat16, device=dev)
+        scale = d ** -0.5
+        ms = _time_events(lambda: attention_ops.multi_query_kv_attention(out, q, k, v, lens, scale), iters=20, warm=5)
+        fl = sum(4 * d * h * (m * (m + 1) // 2) for m in lens)
+        row = {"shape": name, "heads": h, "head_size": d, "prompt_lens": lens, "dtype": "bf16", "ms": ms,
+               "roofline": {"bound": "tensor", "achieved": fl / ms / 1e9, "peak": peak, "unit": "TFLOP/s",
+                            "frac": fl / ms / 1e9 / peak, "traffic": None, "peak_source": peak_src,
+                            "algorithmic_flops_per_launch": fl}}
+        try:
+            b, L = len(lens), lens[0]
+            q4, k4, v4 = (t.reshape(b, L, h, d).transpose(1, 2) for t in (q, k, v))
+            sd = lambda: F.scaled_dot_product_attention(q4, k4, v4, is_causal=True, scale=scale)
+            ref = sd().transpose(1, 2).reshape(n, h, d)
+            ms_sd = _time_events(sd, iters=20, warm=5)
+            row["library_sdpa_ms"] = ms_sd
+            row["library_sdpa_tflops"] = fl / ms_sd / 1e9
+            row["speedup_vs_library"] = ms_sd / ms
+            row["max_abs_diff_vs_library"] = float((ref.float() - out.float()).abs().max())
+        except Exception as e:
+            row["library_sdpa_error"] = repr(e)[:200]
+        rows.append(row)
+        del qkv, out
+        torch.cuda.empty_cache()
+    return rows
 
 
 def main():
@@ -334,8 +693,14 @@ def main():
     ap.add_argument("--workload", default="llama13b_tp", choices=sorted(WORKLOADS))
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true", help="skip the CPU leg (tuning runs)")
-    ap.add_argument("--no-also", action="store_true", help="skip the extra configs[1] measurement at N=1")
+    ap.add_argument("--no-also", action="store_true", help="skip the extra workloads, movers, prefill and all-reduce legs")
+    ap.add_argument("--leg", default="", help=argparse.SUPPRESS)           # child-process legs
+    ap.add_argument("--heads-local", type=int, default=0, help=argparse.SUPPRESS)
+    ap.add_argument("--device-index", type=int, default=0, help=argparse.SUPPRESS)
     args = ap.parse_args()
+    if args.leg == "ref-kernel":
+        ref_kernel_leg(args.workload, args.heads_local or WORKLOADS[args.workload]["heads"], args.device_index)
+        return
     if args.warmup < 3:
         args.warmup = 3
     wl = WORKLOADS[args.workload]
@@ -384,10 +749,19 @@ def main():
 
     p = make_problem(wl, heads_local, dev)
     esize = p["kc"].element_size()
-    ms_k, win_k, launches, _ = run_kernel_steps(p, args.steps, args.warmup, barrier)
+    ms_k, win_k, launches, out = run_kernel_steps(p, args.steps, args.warmup, barrier)
     ms_k = max_over_ranks(ms_k)
+    check = None
+    if rank == 0:      # checker, outside the timed regions: rank 0's shard of the output against the CPU oracle
+        try:
+            check = oracle_row_check(p, out)
+        except Exception as e:
+            check = {"ok": None, "error": repr(e)[:300]}
+    del out
     ms_e, win_e, h2d, d2h = run_e2e_steps(p, args.steps, args.warmup, barrier)
     ms_e = max_over_ranks(ms_e)
+    ms_p, win_p = run_e2e_pipelined(p, args.steps, args.warmup, barrier)
+    ms_p = max_over_ranks(ms_p)
 
     # read ceiling of the kernel's own access pattern (TMA bulk copies, no arithmetic) over the same K pages
     probe_gbs = None
@@ -413,41 +787,63 @@ def main():
     seqs_job = wl["seqs"] if wl["shard"] else wl["seqs"] * n_gpus      # sequences the whole job finishes per step
     t_step = ms_k / args.steps / 1e3
     t_e2e = ms_e / args.steps / 1e3
+    t_pipe = ms_p / args.steps / 1e3
     bytes_gpu = algorithmic_bytes(wl["seqs"], heads_local, wl["head_size"], wl["block_size"], wl["ctx"], esize)
     bytes_job = bytes_gpu * n_gpus
     peak, peak_src = measured_peak()
     achieved = bytes_gpu / t_step / 1e9
     kv_gb = 2 * p["kc"].numel() * esize / 1e9
 
-    also = None
-    if n_gpus == 1 and args.workload == "llama13b_tp" and not args.no_also:
-        del p
-        torch.cuda.empty_cache()
-        wl2 = WORKLOADS["llama7b"]
-        p2 = make_problem(wl2, wl2["heads"], dev)
-        ms2, win2, _, _ = run_kernel_steps(p2, args.steps, args.warmup, barrier)
-        ms2e, win2e, _, _ = run_e2e_steps(p2, args.steps, args.warmup, barrier)
-        b2 = algorithmic_bytes(wl2["seqs"], wl2["heads"], wl2["head_size"], wl2["block_size"], wl2["ctx"], 2)
-        t2 = ms2 / args.steps / 1e3
-        also = {"config": workload_config("llama7b", wl2, 1, wl2["heads"]), "dtype": "fp16",
-                "value": wl2["seqs"] / t2, "unit": "seqs/s", "ms_per_step": t2 * 1e3, "hbm_gbs": b2 / t2 / 1e9,
-                "roofline_frac_of_measured": b2 / t2 / 1e9 / peak, "frac_of_8tbs": b2 / t2 / 1e9 / NOMINAL_HBM_GBS,
-                "e2e_value": wl2["seqs"] / (ms2e / args.steps / 1e3)}
-        del p2
-        torch.cuda.empty_cache()
-
     sampler.stop_flag.set()
     sampler.join(timeout=2)
-    clocks = sampler.summary([win_k, win_e])
+    clocks = sampler.summary([win_k, win_e, win_p])
+    del p
+    torch.cuda.empty_cache()
+
+    def guarded(fn, *a):
+        try:
+            return fn(*a)
+        except Exception as e:        # an extra leg never costs the headline line
+            print(f"[bench] {fn.__name__} failed: {e!r}", file=sys.stderr)
+            return {"error": repr(e)[:300]}
+
+    also = movers = prefill = ref_kernel = allreduce = None
+    extras = args.workload == "llama13b_tp" and not args.no_also
+    if extras and n_gpus == 1:
+        k2 = min(args.steps, 100)
+        also = [guarded(decode_block, name, dev, k2, args.warmup, peak) for name in ("llama7b", "neox20b_tp8", "opt66b_tp8")]
+        movers = guarded(movers_block, dev, peak)
+        prefill = guarded(prefill_block, dev)
+        # config 3 at one GPU is out of the reference kernel's reach (32-bit offsets): configs[1] stands in
+        ref_kernel = gpu_reference_kernel("llama7b", WORKLOADS["llama7b"]["heads"], local)
+    elif extras:
+        if rank == 0:
+            ref_kernel = gpu_reference_kernel(args.workload, heads_local, local)
+        barrier()
+        try:
+            from tools.allreduce_check import run_leg
+            rows = run_leg(rank, world)
+            allreduce = {"what": "row-parallel all-reduce after attention (parallel_state.py:506-556): GraphAllReduce"
+                                 "(2560, 5120, bf16) -> pa_allreduce, vs torch.distributed.all_reduce (NCCL) on the same buffer",
+                         "rows": rows} if rank == 0 else None
+        except Exception as e:
+            print(f"[bench] all-reduce leg failed on rank {rank}: {e!r}", file=sys.stderr)
+            allreduce = {"error": repr(e)[:300]}
 
     cpu_baseline = None
     if rank == 0 and n_gpus == 1 and not args.no_cpu_baseline:
-        nseq, one = cpu_sample_size(wl, budget_s=15.0, cap=64)
+        nseq, one = cpu_sample_size(wl, budget_s=15.0, cap=wl["seqs"])
         sec = time_cpu_reference(wl, nseq)
         cpu_baseline = {"value": nseq / sec, "unit": "seqs/s", "cores": torch.get_num_threads(), "kind": "port",
                         "sample": f"one pass over {nseq} of {wl['seqs']} sequences (all {wl['heads']} heads, "
                                   f"{wl['ctx']}-token contexts), PyTorch loop reference restated in oracle/paged_oracle.py",
                         "seconds": sec, "host_cpus": os.cpu_count()}
+        try:
+            c1 = time_cpu_config1()
+            cpu_baseline["config1_seconds"] = c1["seconds"]
+            cpu_baseline["config1"] = c1
+        except Exception as e:
+            cpu_baseline["config1_error"] = repr(e)[:200]
 
     if rank == 0:
         line = {
@@ -459,19 +855,32 @@ def main():
                            l2=f"inputs larger than L2: {kv_gb:.2f} GB of KV pages per GPU re-read every step vs 126 MB L2"),
             "hbm_gbs": bytes_job / t_step / 1e9, "hbm_frac_of_8tbs": achieved / NOMINAL_HBM_GBS,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": traffic_from_profiles(args.workload), "peak_source": peak_src,
+                         "traffic": traffic_from_profiles(args.workload, heads_local), "peak_source": peak_src,
+                         "frac_note": "the peak is a read+write copy; a read-only stream can exceed it (frac > 1): "
+                                      "frac_of_read_probe and hbm_frac_of_8tbs are the bounded readings",
+                         "frac_of_read_probe": (achieved / probe_gbs) if probe_gbs else None,
                          "algorithmic_bytes_per_launch": bytes_gpu, "kernel": "pa::paged_decode_kernel",
                          "read_probe_gbs": probe_gbs,
                          "read_probe_note": "same TMA bulk-copy pattern with no arithmetic (pa_stream_read_probe): "
                                             "the practical HBM read ceiling on this GPU, measured in this run"},
             "e2e": {"value": seqs_job / t_e2e, "unit": "seqs/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "ms_per_step": t_e2e * 1e3,
-                    "note": "per step: pinned host query + block tables + context lens -> device, operator, output -> "
-                            "pinned host, stream sync; the KV cache is resident worker state"},
-            "gpu_launches": launches, "clocks": clocks, "cpu_baseline": cpu_baseline,
+                    "note": "serial: per step pinned host query + block tables + context lens -> device, operator, "
+                            "output -> pinned host, stream sync; the KV cache is resident worker state",
+                    "pipelined": {"value": seqs_job / t_pipe, "unit": "seqs/s", "ms_per_step": t_pipe * 1e3,
+                                  "note": "same bytes per step; uploads and downloads on their own streams, two staging "
+                                          "arenas: the result of step i is on the host before step i+2 is issued"}},
+            "gpu_launches": launches, "clocks": clocks, "check": check, "cpu_baseline": cpu_baseline,
+            "gpu_reference_kernel": ref_kernel,
         }
         if also is not None:
             line["also"] = also
+        if movers is not None:
+            line["cache_movers"] = movers
+        if prefill is not None:
+            line["prefill"] = prefill
+        if allreduce is not None:
+            line["allreduce"] = allreduce
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()

@@ -67,25 +67,22 @@ def graph_time_us(fn, per_graph=20, replays=10):
     return float(t.item())
 
 
-def main():
-    ap = argparse.ArgumentParser()
-    ap.add_argument("--json", default=os.path.join(ROOT, "gpurun_out", "allreduce_check.json"))
-    args = ap.parse_args()
-    rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
-    torch.cuda.set_device(local)
-    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+def run_leg(rank, world, dtypes=(torch.bfloat16,), hidden=5120, max_tokens=2560, token_counts=(8, 256, 2560),
+            modes=(True, False), emit=None):
+    """Correctness (fp32 sum of the gathered inputs; identical bits on every rank; three launches in a row) and
+    graph-timed device time per call of GraphAllReduce for every (dtype, path, token count), next to NCCL's
+    all_reduce on the same buffer.  Needs an initialised NCCL process group.  Rows are returned on rank 0."""
     from vllm_b200.all_reduce import GraphAllReduce
     rows = []
-    for dtype in (torch.bfloat16, torch.float16, torch.float32):
-        hidden, max_tokens = 5120, 2560
-        for mm in (True, False):
+    for dtype in dtypes:
+        for mm in modes:
             try:
                 ar = GraphAllReduce(max_tokens, hidden, dtype, group=None, use_multimem=mm)
             except RuntimeError as e:
                 if rank == 0:
-                    rows.append({"dtype": str(dtype), "multimem": mm, "skipped": str(e)[:200]})
+                    rows.append({"dtype": str(dtype).split(".")[-1], "multimem": mm, "skipped": str(e)[:200]})
                 continue
-            for tokens in (8, 256, 2560):
+            for tokens in token_counts:
                 g = torch.Generator(device="cuda").manual_seed(1234 + rank)
                 x = ar.buffer[:tokens]
                 src = torch.empty((tokens, hidden), dtype=dtype, device="cuda").normal_(generator=g)
@@ -115,13 +112,28 @@ def main():
                 us_nccl = graph_time_us(lambda: dist.all_reduce(x))
                 if rank == 0:
                     nbytes = tokens * hidden * x.element_size()
-                    row = {"dtype": str(dtype).split(".")[-1], "multimem": mm, "tokens": tokens, "bytes": nbytes,
+                    row = {"dtype": str(dtype).split(".")[-1], "path": "multimem (NVLS)" if mm else "peer loads/stores",
+                           "multimem": mm, "tokens": tokens, "bytes": nbytes,
                            "world": world, "correct_and_identical_on_all_ranks": ok_all, "ours_us": round(us_ours, 2),
                            "nccl_us": round(us_nccl, 2), "speedup_vs_nccl": round(us_nccl / us_ours, 2),
-                           "ours_busbw_gbs": round(2 * (world - 1) / world * nbytes / us_ours / 1e3, 1)}
-                    print(json.dumps(row), flush=True)
+                           "ours_busbw_gbs": round(2 * (world - 1) / world * nbytes / us_ours / 1e3, 1),
+                           "timing": "device time per call, 20 calls captured in one CUDA graph, 10 replays, max over ranks"}
+                    if emit:
+                        emit(row)
                     rows.append(row)
             del ar
+    return rows
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--json", default=os.path.join(ROOT, "gpurun_out", "allreduce_check.json"))
+    args = ap.parse_args()
+    rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+    torch.cuda.set_device(local)
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    rows = run_leg(rank, world, dtypes=(torch.bfloat16, torch.float16, torch.float32),
+                   emit=lambda r: print(json.dumps(r), flush=True))
     if rank == 0:
         os.makedirs(os.path.dirname(args.json), exist_ok=True)
         json.dump(rows, open(args.json, "w"), indent=1)
