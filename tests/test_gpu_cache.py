@@ -57,7 +57,7 @@ def test_golden_reference_outputs(cid):
     (3, 2, 16, 8),            # the reference's shape (test_cache.py:157-162)
     (256, 40, 128, 16),       # config 4 decode step
     (2560, 40, 128, 16),      # config 4 prefill (max_num_batched_tokens)
-    (77, 7, 80, 32), (1, 1, 64, 8), (513, 3, 96, 16),
+    (77, 7, 80, 32), (1, 1, 64, 8), (513, 3, 96, 16), (97, 5, 64, 16), (512, 2, 128, 8), (96, 3, 80, 8),
 ])
 def test_reshape_and_gather(dtype, tokens, heads, head_size, block_size):
     from vllm_b200 import cache_ops
@@ -173,16 +173,18 @@ def test_reshape_and_cache_prefill_runs_and_padding_tokens():
     """Consecutive slots (a prompt filling its blocks in order), runs crossing block boundaries, a ragged
     last tile, and negative slots (skipped)."""
     from vllm_b200 import cache_ops
-    for dtype in (torch.float16, torch.float32):
+    # 203 tokens take the direct kernel (97..512 tokens), 1015 the tile mover with its run-aware lane order
+    for dtype, rep in ((torch.float16, 1), (torch.float32, 1), (torch.float16, 5), (torch.float32, 5)):
         x = pt.pack_factor(dtype)
-        n, h, d, b, nb = 203, 3, 128, 16, 40
+        n, h, d, b, nb = 203 * rep, 3, 128, 16, 40 * rep
         g = torch.Generator().manual_seed(7)
         qkv = torch.randn((n, 3, h, d), generator=g).to(dtype)
         kc = torch.randn((nb, h, d // x, b, x), generator=g).to(dtype)
         vc = torch.randn((nb, h, d, b), generator=g).to(dtype)
-        # three prompts: 100 tokens from slot 37, 60 from slot 320, 43 scattered; a few padding tokens
-        slots = torch.cat([torch.arange(37, 137), torch.arange(320, 380),
-                           torch.randperm(200, generator=g)[:43] + 400]).to(torch.int32)
+        # per repetition three prompts: 100 tokens from slot 37, 60 from slot 320, 43 scattered; a few padding tokens
+        slots = torch.cat([torch.cat([torch.arange(37, 137), torch.arange(320, 380),
+                                      torch.randperm(200, generator=g)[:43] + 400]) + 640 * r
+                           for r in range(rep)]).to(torch.int32)
         slots[[5, 101, 202]] = -1
         wk, wv = kc.clone(), vc.clone()
         c_oracle.reshape_and_cache(qkv[:, 1], qkv[:, 2], wk, wv, slots)
