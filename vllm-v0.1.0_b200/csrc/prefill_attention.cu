@@ -134,12 +134,13 @@ static int make_qkv_map(CUtensorMap* map, const void* base, int dtype, int head_
 }
 
 template <typename T, int DP, bool kPaged>
-static int launch_tc(const CUtensorMap& mq, const CUtensorMap& mk, const CUtensorMap& mv, const PrefillTiles& tiles,
+static int launch_tc(const CUtensorMap& mq, const CUtensorMap& mk, const CUtensorMap& mv, const CUtensorMap& mo,
+                     const PrefillTiles& tiles,
                      int ntiles, const PrefillParams& p, cudaStream_t stream) {
-  constexpr int smem = 6 * (DP / 64) * 128 * 128 + 1024 + 128;
+  constexpr int smem = 6 * (DP / 64) * 128 * 128 + 1024 + 256;
   auto kern = prefill_tc_kernel<T, DP, kPaged>;
   PA_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-  kern<<<p.tile_major ? dim3(ntiles, p.num_heads) : dim3(p.num_heads, ntiles), kPfThreads, smem, stream>>>(mq, mk, mv, tiles, p);
+  kern<<<p.tile_major ? dim3(ntiles, p.num_heads) : dim3(p.num_heads, ntiles), kPfThreads, smem, stream>>>(mq, mk, mv, mo, tiles, p);
   count_launch();
   return check_cuda(cudaGetLastError(), "prefill_tc_kernel launch");
 }
@@ -204,13 +205,14 @@ static int prefill(void* out, const void* query, const void* key, const void* va
   if (all.empty()) return PA_OK;
   std::stable_sort(all.begin(), all.end(), [](const Tile& a, const Tile& b) { return a.span > b.span; });
 
-  CUtensorMap mq, mk, mv;
+  CUtensorMap mq, mk, mv, mo;
   const int dp = head_size <= 64 ? 64 : 128;
   if (dtype != PA_F32) {
     int rc = make_qkv_map(&mq, query, dtype, head_size, num_heads, tok, q_stride);
     if (paged) { mk = mq; mv = mq; }               // unused by the paged kernel
     if (rc == PA_OK && !paged) rc = make_qkv_map(&mk, key, dtype, head_size, num_heads, ktok, k_stride);
     if (rc == PA_OK && !paged) rc = make_qkv_map(&mv, value, dtype, head_size, num_heads, ktok, v_stride);
+    if (rc == PA_OK) rc = make_qkv_map(&mo, out, dtype, head_size, num_heads, tok, out_stride);
     if (rc != PA_OK) return rc;
   }
   PrefillParams p;
@@ -218,6 +220,7 @@ static int prefill(void* out, const void* query, const void* key, const void* va
   p.scale_log2 = scale * 1.4426950408889634f; p.dbg = dbg;
   // K/V bytes of the batch against the L2 (126 MB on B200): beyond it, query tiles of one head run together
   p.tile_major = ktok * num_heads * head_size * 4 > (int64_t{96} << 20);
+  { const char* e = getenv("PA_PREFILL_FREERUN"); p.free_run = e ? atoi(e) : 0; }
   p.key_cache = nullptr; p.value_cache = nullptr; p.block_tables = nullptr; p.max_blocks = 0; p.block_shift = 0;
   if (paged) {
     p.key_cache = paged->key_cache; p.value_cache = paged->value_cache; p.block_tables = paged->block_tables;
@@ -241,12 +244,12 @@ static int prefill(void* out, const void* query, const void* key, const void* va
         default:  rc = launch_f32<128>(query, key, value, out, q_stride, k_stride, v_stride, out_stride, tiles, n, num_heads, p.scale_log2, stream); break;
       }
     } else if (paged) {
-      if (dtype == PA_F16) rc = dp == 64 ? launch_tc<F16, 64, true>(mq, mk, mv, tiles, n, p, stream) : launch_tc<F16, 128, true>(mq, mk, mv, tiles, n, p, stream);
-      else rc = dp == 64 ? launch_tc<BF16, 64, true>(mq, mk, mv, tiles, n, p, stream) : launch_tc<BF16, 128, true>(mq, mk, mv, tiles, n, p, stream);
+      if (dtype == PA_F16) rc = dp == 64 ? launch_tc<F16, 64, true>(mq, mk, mv, mo, tiles, n, p, stream) : launch_tc<F16, 128, true>(mq, mk, mv, mo, tiles, n, p, stream);
+      else rc = dp == 64 ? launch_tc<BF16, 64, true>(mq, mk, mv, mo, tiles, n, p, stream) : launch_tc<BF16, 128, true>(mq, mk, mv, mo, tiles, n, p, stream);
     } else if (dtype == PA_F16) {
-      rc = dp == 64 ? launch_tc<F16, 64, false>(mq, mk, mv, tiles, n, p, stream) : launch_tc<F16, 128, false>(mq, mk, mv, tiles, n, p, stream);
+      rc = dp == 64 ? launch_tc<F16, 64, false>(mq, mk, mv, mo, tiles, n, p, stream) : launch_tc<F16, 128, false>(mq, mk, mv, mo, tiles, n, p, stream);
     } else {
-      rc = dp == 64 ? launch_tc<BF16, 64, false>(mq, mk, mv, tiles, n, p, stream) : launch_tc<BF16, 128, false>(mq, mk, mv, tiles, n, p, stream);
+      rc = dp == 64 ? launch_tc<BF16, 64, false>(mq, mk, mv, mo, tiles, n, p, stream) : launch_tc<BF16, 128, false>(mq, mk, mv, mo, tiles, n, p, stream);
     }
     if (rc != PA_OK) return rc;
     p.dbg = nullptr;

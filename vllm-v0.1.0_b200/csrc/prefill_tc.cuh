@@ -53,6 +53,7 @@ struct PrefillParams {
   // 1: grid (tile, head) -- for batches whose K/V exceeds L2.  Measured on B200: 8 x 4096 tokens 948 -> 1064
   // TFLOP/s with 1, 5 x 512 tokens 317 -> 304 and a ragged 2560-token batch 418 -> 360 with it.
   int32_t tile_major;
+  int32_t free_run;   // experiment: the issuer does not wait for P, the softmax groups skip their loop (wrong results, tensor-only timing)
 };
 
 constexpr int kPfPageThreads = 96;   // warps 8, 10 and 11 copy pages when kPaged
@@ -67,6 +68,17 @@ __device__ __forceinline__ void cp_async_arrive(uint32_t bar) {
   asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" :: "r"(bar) : "memory");
 }
 
+
+// tests / tools: SM-clock stamps of the hand-offs of CTA (head 0, tile 0) into the debug buffer, after the raw
+// tiles: slot ((who * kTlIters + j) * 8 + event), who = 0 / 1 softmax group A / B, 2 issuer (tools/prefill_timeline.py)
+constexpr int kTlBase = 40000, kTlIters = 40;
+__device__ __forceinline__ void stamp(float* dbg, bool on, int who, int j, int ev) {
+  if (on && j < kTlIters) {
+    uint32_t c;
+    asm volatile("mov.u32 %0, %%clock;" : "=r"(c));
+    reinterpret_cast<uint32_t*>(dbg)[kTlBase + (who * kTlIters + j) * 8 + ev] = c;
+  }
+}
 
 __device__ __forceinline__ float ex2(float x) {   // exp2(-inf) == 0
   float y;
@@ -102,12 +114,14 @@ __device__ __forceinline__ void fadd2(float& a0, float& a1, float b0, float b1) 
 // Named barriers 1 and 2 hand the special-function unit back and forth between the two softmax groups
 // (bar.sync by the 128 threads that wait, bar.arrive by the 128 that release).
 __device__ __forceinline__ void named_sync(int id) { asm volatile("bar.sync %0, 256;" :: "r"(id) : "memory"); }
+__device__ __forceinline__ void named_sync_n(int id, int n) { asm volatile("bar.sync %0, %1;" :: "r"(id), "r"(n) : "memory"); }
 __device__ __forceinline__ void named_arrive(int id) { asm volatile("bar.arrive %0, 256;" :: "r"(id) : "memory"); }
 
 template <typename T, int DP, bool kPaged = false>
 __global__ void __launch_bounds__(kPfThreads, 1)
 prefill_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant__ CUtensorMap tmk,
-                  const __grid_constant__ CUtensorMap tmv, const __grid_constant__ PrefillTiles tiles,
+                  const __grid_constant__ CUtensorMap tmv, const __grid_constant__ CUtensorMap tmo,
+                  const __grid_constant__ PrefillTiles tiles,
                   const PrefillParams p) {
   constexpr int kAtoms = DP / 64;                 // 64-element (128-byte) column groups of a tile
   constexpr uint32_t kAtomBytes = 128 * 128;      // 128 rows x 128 bytes
@@ -132,6 +146,7 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant
   const uint32_t bar_q = sBar;                     // Q tiles landed
   const uint32_t bar_kf = sBar + 8, bar_ke = sBar + 24, bar_vf = sBar + 40, bar_ve = sBar + 56;   // [2] each
   const uint32_t bar_s = sBar + 72, bar_p = sBar + 88, bar_o = sBar + 104;                        // [2] each
+  const uint32_t bar_ph = sBar + 128;              // [2]: the first half of P_i (keys 0-63 of the tile) is in tensor memory
   const uint32_t tm_slot = sBar + 120;
   const uint32_t sc_slot = sBar + 124;             // scale_log2, re-read after the ping-pong barrier (see below)
 
@@ -149,13 +164,16 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant
   const int nB = (q0 + 128 < qlen) ? min(q0 + 255 + koff, klen - 1) / kPfCols + 1 : 0;
   const int nmax = nB > nA ? nB : nA;
 
+  stamp(p.dbg, p.dbg && head == 0 && tile == 0 && tid == 0, 2, kTlIters - 2, 7);   // kernel entry
   if (tid == 0) {
     tc05::tma_prefetch_desc(&tmq); tc05::tma_prefetch_desc(&tmk); tc05::tma_prefetch_desc(&tmv);
+    tc05::tma_prefetch_desc(&tmo);
     mbar_init(bar_q, 1);
     for (int s = 0; s < 2; ++s) {
       mbar_init(bar_kf + 8 * s, kPaged ? kPfPageThreads : 1); mbar_init(bar_ke + 8 * s, 1);
       mbar_init(bar_vf + 8 * s, kPaged ? kPfPageThreads : 1); mbar_init(bar_ve + 8 * s, 1);
       mbar_init(bar_s + 8 * s, 1); mbar_init(bar_p + 8 * s, 128); mbar_init(bar_o + 8 * s, 1);
+      mbar_init(bar_ph + 8 * s, 128);
     }
     asm volatile("st.shared.f32 [%0], %1;" :: "r"(sc_slot), "f"(p.scale_log2) : "memory");
     mbar_init_fence();
@@ -286,57 +304,77 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant
   } else if (warp == 9) {
     // ===================== MMA issuer =====================
     asm volatile("setmaxnreg.dec.sync.aligned.u32 56;");
-    if (lane == 0) {
-      auto issue_qk = [&](int i, int j) {           // S_i = Q_i . K_j^T
-        const uint32_t qb = sQ + i * kTileBytes, kb = sK + (j & 1) * kTileBytes;
+    // The whole warp runs this loop converged (all lanes poll the barriers); one pre-elected lane issues.
+    // Descriptors: one 32-bit add on the low word of a per-tile base (the start-address field, bytes >> 4).
+    const bool leader = tc05::elect_one();
+    const uint32_t tm = __shfl_sync(0xffffffffu, tmem, 0);
+    const bool tl = p.dbg && head == 0 && tile == 0 && lane == 0;
+    auto desc = [](uint64_t base, uint32_t byte_off) { return base + (byte_off >> 4); };
+    const uint64_t dq = tc05::smem_desc_sw128(sQ, 16, 1024), dk = tc05::smem_desc_sw128(sK, 16, 1024);
+    const uint64_t dv = kPaged ? tc05::smem_desc_sw128(sV, 16, 1024) : tc05::smem_desc_sw128(sV, kAtomBytes, 1024);
+    auto issue_qk = [&](int i, int j) {             // S_i = Q_i . K_j^T
+      const uint64_t qb = desc(dq, i * kTileBytes), kb = desc(dk, (j & 1) * kTileBytes);
 #pragma unroll
-        for (int kk = 0; kk < DP / 16; ++kk) {
-          if (kk >= qk_steps) break;
-          const uint32_t off = (kk >> 2) * kAtomBytes + (kk & 3) * 32;
-          tc05::mma_ss(tmem + kTmS + 128 * i, tc05::smem_desc_sw128(qb + off, 16, 1024),
-                       tc05::smem_desc_sw128(kb + off, 16, 1024), kIdescQK, kk > 0);
-        }
-      };
-      auto issue_pv = [&](int i, int j) {           // O_i (+)= P_i . V_j
-        const uint32_t vb = sV + (j & 1) * kTileBytes;
-#pragma unroll
-        for (int kk = 0; kk < kPfCols / 16; ++kk) {
-          const uint64_t vdesc = kPaged ? tc05::smem_desc_sw128(vb + (kk >> 2) * kVAtomBytes + (kk & 3) * 32, 16, 1024)
-                                        : tc05::smem_desc_sw128(vb + kk * 2048, kAtomBytes, 1024);
-          tc05::mma_ts(tmem + kTmO + 128 * i, tmem + kTmS + 128 * i + kk * 8, vdesc, idesc_pv, j > 0 || kk > 0);
-        }
-      };
-      mbar_wait(bar_q, 0);
-      mbar_wait(bar_kf, 0);
-      if (kPaged) tc05::fence_async_smem();         // cp.async wrote through the generic proxy
-      tc05::fence_after_sync();
-      issue_qk(0, 0);
-      tc05::mma_commit(bar_s);
-      if (nB) { issue_qk(1, 0); tc05::mma_commit(bar_s + 8); }
-      tc05::mma_commit(bar_ke);                     // K_0 is free once these have run
-      for (int j = 0; j < nmax; ++j) {
-        const int s = j & 1;
-        const bool more_k = j + 1 < nmax;
-        if (more_k) { mbar_wait(bar_kf + 8 * (s ^ 1), ((j + 1) >> 1) & 1); }
-        mbar_wait(bar_vf + 8 * s, (j >> 1) & 1);
-        if (kPaged) tc05::fence_async_smem();
-#pragma unroll
-        for (int i = 0; i < 2; ++i) {
-          const int ni = i ? nB : nA;
-          if (j < ni) {
-            mbar_wait(bar_p + 8 * i, j & 1);         // P_i of tile j is in tensor memory
-            tc05::fence_after_sync();
-            issue_pv(i, j);
-            if (j + 1 < ni) { issue_qk(i, j + 1); tc05::mma_commit(bar_s + 8 * i); }
-            else tc05::mma_commit(bar_o + 8 * i);
-          }
-        }
-        tc05::mma_commit(bar_ve + 8 * s);            // V_j and K_{j+1} are consumed by everything issued so far
-        if (more_k) tc05::mma_commit(bar_ke + 8 * (s ^ 1));
+      for (int kk = 0; kk < DP / 16; ++kk) {
+        if (kk >= qk_steps) break;
+        const uint32_t off = (kk >> 2) * kAtomBytes + (kk & 3) * 32;
+        tc05::mma_ss_w(leader, tm + kTmS + 128 * i, desc(qb, off), desc(kb, off), kIdescQK, kk > 0);
       }
-      // the last commit must have landed in this CTA's shared memory before the CTA may exit
-      mbar_wait(bar_ve + 8 * ((nmax - 1) & 1), ((nmax - 1) >> 1) & 1);
+    };
+    auto issue_pv = [&](int i, int j, int half) {   // O_i (+)= P_i . V_j, keys 64 half .. 64 half + 63 of the tile
+      const uint64_t vb = desc(dv, (j & 1) * kTileBytes);
+#pragma unroll
+      for (int kk = half * (kPfCols / 32); kk < (half + 1) * (kPfCols / 32); ++kk) {
+        const uint32_t off = kPaged ? (kk >> 2) * kVAtomBytes + (kk & 3) * 32 : kk * 2048;
+        tc05::mma_ts_w(leader, tm + kTmO + 128 * i, tm + kTmS + 128 * i + kk * 8, desc(vb, off), idesc_pv, j > 0 || kk > 0);
+      }
+    };
+    mbar_wait(bar_q, 0);
+    mbar_wait(bar_kf, 0);
+    stamp(p.dbg, tl, 2, 0, 6);
+    if (kPaged) tc05::fence_async_smem();           // cp.async wrote through the generic proxy
+    tc05::fence_after_sync();
+    issue_qk(0, 0);
+    tc05::mma_commit_w(leader, bar_s);
+    if (nB) { issue_qk(1, 0); tc05::mma_commit_w(leader, bar_s + 8); }
+    tc05::mma_commit_w(leader, bar_ke);             // K_0 is free once these have run
+    for (int j = 0; j < nmax; ++j) {
+      const int s = j & 1;
+      const bool more_k = j + 1 < nmax;
+      mbar_wait(bar_vf + 8 * s, (j >> 1) & 1);
+      if (kPaged) tc05::fence_async_smem();
+      stamp(p.dbg, tl, 2, j, 4);
+#pragma unroll
+      for (int i = 0; i < 2; ++i) {
+        const int ni = i ? nB : nA;
+        if (j < ni) {
+          // P_i of tile j arrives in two halves: the first half's product runs while the softmax group is
+          // still in the exponentials of the second
+          if (!(p.free_run & 1)) mbar_wait(bar_ph + 8 * i, j & 1);
+          tc05::fence_after_sync();
+          stamp(p.dbg, tl, 2, j, 2 * i);
+          issue_pv(i, j, 0);
+          if (!(p.free_run & 1)) mbar_wait(bar_p + 8 * i, j & 1);
+          tc05::fence_after_sync();
+          issue_pv(i, j, 1);
+          if (j + 1 < ni) {
+            if (i == 0 || j + 1 >= nA) {            // K_{j+1} is needed from here on, not before the P.V above
+              mbar_wait(bar_kf + 8 * (s ^ 1), ((j + 1) >> 1) & 1);
+              if (kPaged) tc05::fence_async_smem();
+            }
+            issue_qk(i, j + 1);
+            tc05::mma_commit_w(leader, bar_s + 8 * i);
+          } else {
+            tc05::mma_commit_w(leader, bar_o + 8 * i);
+          }
+          stamp(p.dbg, tl, 2, j, 2 * i + 1);
+        }
+      }
+      tc05::mma_commit_w(leader, bar_ve + 8 * s);   // V_j and K_{j+1} are consumed by everything issued so far
+      if (more_k) tc05::mma_commit_w(leader, bar_ke + 8 * (s ^ 1));
     }
+    // the last commit must have landed in this CTA's shared memory before the CTA may exit
+    mbar_wait(bar_ve + 8 * ((nmax - 1) & 1), ((nmax - 1) >> 1) & 1);
   } else if (warp >= 10) {
     // register donors.  384 threads x 168 registers is the CTA's pool = 128 x 56 + 256 x 224; setmaxnreg must be
     // the same instruction in all four warps of a warpgroup (warps 8-11), whatever branch they sit in
@@ -350,19 +388,22 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant
     const int qi0 = q0 + 128 * grp;                 // first row of this tile inside the prompt
     const uint32_t lane_base = tmem + (static_cast<uint32_t>((warp & 3) * 32) << 16);
     const uint32_t tS = lane_base + kTmS + 128 * grp, tO = lane_base + kTmO + 128 * grp;
-    const bool dump = p.dbg && head == 0 && tile == 0 && grp == 0;
+    const bool dump = p.dbg && head == 0 && tile == 0 && grp == 0 && !(p.free_run & 4);   // 4: stamps only
+    const bool tl = p.dbg && head == 0 && tile == 0 && r == 0;
     float m_run = -CUDART_INF_F, l_run = 0.f;
     // The exponentials of a tile keep the SM's special-function unit busy for as long as the tensor core
     // needs for that tile's two matrix products.  Left alone, the two groups drift into phase -- both in
     // their exponentials (sharing the unit), then both waiting for the tensor core -- and each unit idles
     // half of the time.  So the exponential section is a critical section that alternates A, B, A, B, ...:
     // while one group is in it the tensor core runs the other tile's P.V and next Q.K^T.
-    const bool pingpong = nB > 0;
+    const bool pingpong = nB > 0 && !(p.free_run & 2);
     const int bar_mine = 1 + grp, bar_other = 2 - grp;
     if (pingpong && grp == 1) named_arrive(bar_other);          // A goes first
-    for (int j = 0; j < ni; ++j) {
+    for (int j = 0; j < ((p.free_run & 1) ? 0 : ni); ++j) {
+      stamp(p.dbg, tl, grp, j, 0);
       mbar_wait(bar_s + 8 * grp, j & 1);
       tc05::fence_after_sync();
+      stamp(p.dbg, tl, grp, j, 1);
       uint32_t s[4][32];
 #pragma unroll
       for (int c = 0; c < 4; ++c) tc05::tmem_ld32(tS + c * 32, s[c]);
@@ -416,11 +457,13 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant
       }
       const float neg_m = -m_run;
       float sum[4] = {0.f, 0.f, 0.f, 0.f};
+      stamp(p.dbg, tl, grp, j, 2);
       if (pingpong && j < nA) named_sync(bar_mine);   // B's extra (diagonal) tile runs after A's last: no turn to wait for
       // ptxas moves arithmetic (and MUFU) across BAR.SYNC freely; what it cannot move is a value loaded
       // after the barrier, so the section's multiplier is re-read from shared memory here
       float sc;
       asm volatile("ld.volatile.shared.f32 %0, [%1];" : "=f"(sc) : "r"(sc_slot) : "memory");
+      stamp(p.dbg, tl, grp, j, 3);
 #pragma unroll
       for (int c2 = 0; c2 < 2; ++c2) {
         uint32_t pk[32];
@@ -435,7 +478,14 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant
             pk[h * 16 + (i >> 1)] = pack2<T>(p0, p1);
           }
         tc05::tmem_st32(tS + c2 * 32, pk);
+        if (c2 == 0) {                                // keys 0-63 of P: the issuer starts P.V on them
+          tc05::tmem_wait_st();
+          tc05::fence_before_sync();
+          mbar_arrive(bar_ph + 8 * grp);
+          stamp(p.dbg, tl, grp, j, 7);
+        }
       }
+      stamp(p.dbg, tl, grp, j, 4);
       // hand over: B after its tile j lets A into tile j + 1 (if A has one); A after tile j lets B into tile j.
       // Every arrive is matched by exactly one later sync of the other group before the next arrive on the same
       // barrier can happen (two back-to-back arrives would complete the barrier with nobody waiting).
@@ -444,16 +494,22 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant
       tc05::tmem_wait_st();
       tc05::fence_before_sync();
       mbar_arrive(bar_p + 8 * grp);
+      stamp(p.dbg, tl, grp, j, 5);
     }
     if (ni > 0) {
       // ---- epilogue: O / l -> out ---------------------------------------------------------
+      stamp(p.dbg, tl, grp, kTlIters - 1, 0);
       mbar_wait(bar_o + 8 * grp, 0);
       tc05::fence_after_sync();
+      stamp(p.dbg, tl, grp, kTlIters - 1, 1);
+      // Every thread holds one row of O; stored from here, a warp's 16-byte stores would land in 32 different
+      // rows (32 wavefronts per instruction: measured 4400 clk for the tile).  So the tile is staged in shared
+      // memory -- the Q tile's slot, free since this tile's last Q.K^T, in the same 128-byte-swizzled layout --
+      // and leaves as one TMA store per 64-column group; a prompt's last, partial tile (rows past the prompt
+      // belong to the next one) leaves as row-contiguous 16-byte stores of its valid rows instead.
       const int D = p.head_size;
-      const bool row_ok = qi0 + r < qlen;
       const float inv = 1.f / l_run;
-      char* orow = reinterpret_cast<char*>(p.out) +
-                   ((static_cast<int64_t>(qtok0) + qi0 + r) * p.out_stride + static_cast<int64_t>(head) * D) * 2;
+      const uint32_t stg = sQ + grp * kTileBytes;
 #pragma unroll
       for (int c = 0; c < DP / 32; ++c) {
         uint32_t o[32];
@@ -464,24 +520,46 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant
           for (int i = 0; i < 32; ++i) p.dbg[128 * 128 + r * DP + c * 32 + i] = __uint_as_float(o[i]);
           if (c == 0) { p.dbg[128 * 128 + 128 * DP + r] = l_run; p.dbg[128 * 128 + 128 * DP + 128 + r] = m_run; }
         }
-        if (row_ok) {
 #pragma unroll
-          for (int v = 0; v < 4; ++v) {               // 8 elements = 16 bytes per store
-            if (c * 32 + v * 8 < D) {
-              uint4 w;
-              w.x = pack2<T>(__uint_as_float(o[v * 8 + 0]) * inv, __uint_as_float(o[v * 8 + 1]) * inv);
-              w.y = pack2<T>(__uint_as_float(o[v * 8 + 2]) * inv, __uint_as_float(o[v * 8 + 3]) * inv);
-              w.z = pack2<T>(__uint_as_float(o[v * 8 + 4]) * inv, __uint_as_float(o[v * 8 + 5]) * inv);
-              w.w = pack2<T>(__uint_as_float(o[v * 8 + 6]) * inv, __uint_as_float(o[v * 8 + 7]) * inv);
-              *reinterpret_cast<uint4*>(orow + (c * 32 + v * 8) * 2) = w;
-            }
-          }
+        for (int v = 0; v < 4; ++v) {                 // 8 elements = one 16-byte chunk
+          const uint32_t w0 = pack2<T>(__uint_as_float(o[v * 8 + 0]) * inv, __uint_as_float(o[v * 8 + 1]) * inv);
+          const uint32_t w1 = pack2<T>(__uint_as_float(o[v * 8 + 2]) * inv, __uint_as_float(o[v * 8 + 3]) * inv);
+          const uint32_t w2 = pack2<T>(__uint_as_float(o[v * 8 + 4]) * inv, __uint_as_float(o[v * 8 + 5]) * inv);
+          const uint32_t w3 = pack2<T>(__uint_as_float(o[v * 8 + 6]) * inv, __uint_as_float(o[v * 8 + 7]) * inv);
+          const uint32_t chunk = (c & 1) * 4 + v;
+          const uint32_t dst = stg + (c >> 1) * kAtomBytes + r * 128 + ((chunk ^ (r & 7)) << 4);
+          asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" :: "r"(dst), "r"(w0), "r"(w1), "r"(w2), "r"(w3) : "memory");
+        }
+      }
+      const int valid = min(128, qlen - qi0);         // rows of this tile inside the prompt
+      if (valid == 128) {
+        tc05::fence_async_smem();
+        named_sync_n(3 + grp, 128);
+        if (r == 0) {
+#pragma unroll
+          for (int a = 0; a < kAtoms; ++a)
+            if (a * 64 < D) tc05::tma_store_3d(&tmo, stg + a * kAtomBytes, a * 64, head, qtok0 + qi0);
+          tc05::tma_store_commit();
+          tc05::tma_store_wait_read();
+        }
+      } else {
+        named_sync_n(3 + grp, 128);
+        const int cpr = D / 8;                        // 16-byte chunks per row: 8, 10, 12 or 16
+        char* obase = reinterpret_cast<char*>(p.out) +
+                      ((static_cast<int64_t>(qtok0) + qi0) * p.out_stride + static_cast<int64_t>(head) * D) * 2;
+        for (int idx = r; idx < valid * cpr; idx += 128) {
+          const int row = idx / cpr, chunk = idx - row * cpr;
+          const uint32_t src = stg + (chunk >> 3) * kAtomBytes + row * 128 + (((chunk & 7) ^ (row & 7)) << 4);
+          uint4 w;
+          asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(w.x), "=r"(w.y), "=r"(w.z), "=r"(w.w) : "r"(src) : "memory");
+          *reinterpret_cast<uint4*>(obase + static_cast<int64_t>(row) * p.out_stride * 2 + chunk * 16) = w;
         }
       }
     }
   }
   tc05::fence_before_sync();
   __syncthreads();
+  stamp(p.dbg, p.dbg && head == 0 && tile == 0 && tid == 0, 2, kTlIters - 1, 7);   // all warps done
   if (warp == 0) tc05::tmem_free<kTmCols>(tmem);
 }
 
