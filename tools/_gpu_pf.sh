@@ -1,7 +1,5 @@
 mkdir -p gpurun_out
-timeout 900 python -m pytest tests/test_prefill.py tests/test_cached_prefill.py tests/test_gpu_layer.py -m gpu -x -q 2>&1 | tail -6
-PA_PREFILL_FREERUN=4 python tools/prefill_timeline.py 4096 8 2>&1 | tail -3
-PA_PREFILL_FREERUN=4 python tools/prefill_timeline.py 512 5 2>&1 | tail -3
+timeout 600 python -m pytest tests/test_prefill.py tests/test_cached_prefill.py tests/test_gpu_layer.py -m gpu -x -q 2>&1 | tail -15
 timeout 300 python tools/prefill_bench.py 2>&1 | python -c "
 import sys, json
 for l in sys.stdin:

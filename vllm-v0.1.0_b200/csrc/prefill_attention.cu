@@ -137,7 +137,7 @@ template <typename T, int DP, bool kPaged>
 static int launch_tc(const CUtensorMap& mq, const CUtensorMap& mk, const CUtensorMap& mv, const CUtensorMap& mo,
                      const PrefillTiles& tiles,
                      int ntiles, const PrefillParams& p, cudaStream_t stream) {
-  constexpr int smem = 6 * (DP / 64) * 128 * 128 + 1024 + 256;
+  constexpr int smem = 7 * (DP / 64) * 128 * 128 + 1024 + 256;   // Q x 2, K x 2, V x 2, output staging; alignment slack; barriers
   auto kern = prefill_tc_kernel<T, DP, kPaged>;
   PA_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
   kern<<<p.tile_major ? dim3(ntiles, p.num_heads) : dim3(p.num_heads, ntiles), kPfThreads, smem, stream>>>(mq, mk, mv, mo, tiles, p);
@@ -220,7 +220,6 @@ static int prefill(void* out, const void* query, const void* key, const void* va
   p.scale_log2 = scale * 1.4426950408889634f; p.dbg = dbg;
   // K/V bytes of the batch against the L2 (126 MB on B200): beyond it, query tiles of one head run together
   p.tile_major = ktok * num_heads * head_size * 4 > (int64_t{96} << 20);
-  { const char* e = getenv("PA_PREFILL_FREERUN"); p.free_run = e ? atoi(e) : 0; }
   p.key_cache = nullptr; p.value_cache = nullptr; p.block_tables = nullptr; p.max_blocks = 0; p.block_shift = 0;
   if (paged) {
     p.key_cache = paged->key_cache; p.value_cache = paged->value_cache; p.block_tables = paged->block_tables;

@@ -12,6 +12,14 @@
 // the issuer interleaves the chains of A and B, so the tensor core works on one tile's matrices
 // while the other tile's threads are in their softmax.  tcgen05.mma executes in issue order, which
 // is what makes the S_i / P_i aliasing safe without an extra barrier.
+//
+// CTAs are persistent by work stealing: the grid still has one CTA per (tile, head) in the host's order, but a
+// running CTA cancels the next pending one (cluster launch control) and takes over its blockIdx, so every role
+// loops over work items.  Measured before (tools/prefill_timeline.py): 5400 clk from CTA entry to the first MMA
+// (barrier init, TMEM allocation, Q / K_0 from HBM) and 3000-4400 clk from the last P.V to exit, with the
+// tensor core idle in both; per item now the producer has Q and K_0 / V_0 of the NEXT item in shared memory
+// before the current one ends (the rings simply continue), the issuer runs the next item's first Q.K^T behind
+// the last P.V, and the output tile leaves through its own staging buffer.
 #pragma once
 
 #include <math_constants.h>
@@ -53,7 +61,6 @@ struct PrefillParams {
   // 1: grid (tile, head) -- for batches whose K/V exceeds L2.  Measured on B200: 8 x 4096 tokens 948 -> 1064
   // TFLOP/s with 1, 5 x 512 tokens 317 -> 304 and a ragged 2560-token batch 418 -> 360 with it.
   int32_t tile_major;
-  int32_t free_run;   // experiment: the issuer does not wait for P, the softmax groups skip their loop (wrong results, tensor-only timing)
 };
 
 constexpr int kPfPageThreads = 96;   // warps 8, 10 and 11 copy pages when kPaged
@@ -142,38 +149,76 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant
   const uint32_t sQ = base;                        // two tiles
   const uint32_t sK = sQ + 2 * kTileBytes;         // two stages
   const uint32_t sV = sK + 2 * kTileBytes;         // two stages
-  const uint32_t sBar = sV + 2 * kTileBytes;
+  const uint32_t sStg = sV + 2 * kTileBytes;       // output tile on its way out (one group at a time)
+  const uint32_t sBar = sStg + kTileBytes;
   const uint32_t bar_q = sBar;                     // Q tiles landed
   const uint32_t bar_kf = sBar + 8, bar_ke = sBar + 24, bar_vf = sBar + 40, bar_ve = sBar + 56;   // [2] each
   const uint32_t bar_s = sBar + 72, bar_p = sBar + 88, bar_o = sBar + 104;                        // [2] each
   const uint32_t bar_ph = sBar + 128;              // [2]: the first half of P_i (keys 0-63 of the tile) is in tensor memory
+  const uint32_t bar_qe = sBar + 144;              // the item's last Q.K^T has run: the Q tiles may be overwritten
+  const uint32_t bar_stg = sBar + 152;             // the staging buffer's previous user is done with it
+  const uint32_t bar_cf = sBar + 160, bar_ce = sBar + 176;   // [2] each: next work item landed / read by everybody
+  const uint32_t sClc = sBar + 192;                // [2] x 16 bytes: the scheduler's answers
   const uint32_t tm_slot = sBar + 120;
   const uint32_t sc_slot = sBar + 124;             // scale_log2, re-read after the ping-pong barrier (see below)
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+
+  // ---- work items ------------------------------------------------------------------------------------
   // grid order (host's choice, see PrefillParams::tile_major): tiles fastest keeps the CTAs that run together on
   // few heads, so a head's K/V is read from HBM once and from L2 by its other query tiles
-  const int head = p.tile_major ? blockIdx.y : blockIdx.x;
-  const int tile = p.tile_major ? blockIdx.x : blockIdx.y;
-  const int qtok0 = tiles.qtok0[tile], qlen = tiles.qlen[tile], q0 = tiles.q0[tile];
-  const int ktok0 = tiles.ktok0[tile], klen = tiles.klen[tile];
-  const int koff = klen - qlen;                   // keys in front of the first query row
-  // K/V tiles each query tile visits: everything up to and including the tile that holds the last key its
-  // last row sees (plain prompts: its diagonal tile).  nB is nA or nA + 1.
-  const int nA = min(q0 + 127 + koff, klen - 1) / kPfCols + 1;
-  const int nB = (q0 + 128 < qlen) ? min(q0 + 255 + koff, klen - 1) / kPfCols + 1 : 0;
-  const int nmax = nB > nA ? nB : nA;
+  struct Item {
+    int head, tile, qtok0, qlen, q0, ktok0, klen, koff, nA, nB, nmax;
+  };
+  auto decode = [&](int bx, int by) {
+    Item it;
+    it.head = p.tile_major ? by : bx;
+    it.tile = p.tile_major ? bx : by;
+    it.qtok0 = tiles.qtok0[it.tile]; it.qlen = tiles.qlen[it.tile]; it.q0 = tiles.q0[it.tile];
+    it.ktok0 = tiles.ktok0[it.tile]; it.klen = tiles.klen[it.tile];
+    it.koff = it.klen - it.qlen;                  // keys in front of the first query row
+    // K/V tiles each query tile visits: everything up to and including the tile that holds the last key its
+    // last row sees (plain prompts: its diagonal tile).  nB is nA or nA + 1.
+    it.nA = min(it.q0 + 127 + it.koff, it.klen - 1) / kPfCols + 1;
+    it.nB = (it.q0 + 128 < it.qlen) ? min(it.q0 + 255 + it.koff, it.klen - 1) / kPfCols + 1 : 0;
+    it.nmax = it.nB > it.nA ? it.nB : it.nA;
+    return it;
+  };
+  // Item n + 1 of this CTA is the answer to the n-th request (slot n & 1), issued by the scheduler thread when
+  // it starts item n.  Every thread that works on items calls next_item() once per item, in order: it waits for
+  // the answer, reads it, releases the slot, and learns whether to go on.
+  constexpr uint32_t kClcReaders = 256 + 1 + (kPaged ? kPfPageThreads : 1);   // softmax threads, issuer lane, producers
+  auto request_next = [&](int n) {                // scheduler thread only
+    const uint32_t slot = n & 1;
+    mbar_wait(bar_ce + 8 * slot, ((n >> 1) & 1) ^ 1);   // first use of a slot passes immediately
+    mbar_expect_tx(bar_cf + 8 * slot, 16);
+    tc05::clc_try_cancel(sClc + 16 * slot, bar_cf + 8 * slot);
+  };
+  auto next_item = [&](int n, Item& it, bool arrive) {
+    const uint32_t slot = n & 1;
+    mbar_wait(bar_cf + 8 * slot, (n >> 1) & 1);
+    int bx, by;
+    const bool ok = tc05::clc_read(sClc + 16 * slot, bx, by);
+    tc05::fence_async_smem();                     // my read is ordered before the slot's next asynchronous write
+    if (arrive) mbar_arrive(bar_ce + 8 * slot);
+    if (ok) it = decode(bx, by);
+    return ok;
+  };
+  Item it = decode(blockIdx.x, blockIdx.y);
 
-  stamp(p.dbg, p.dbg && head == 0 && tile == 0 && tid == 0, 2, kTlIters - 2, 7);   // kernel entry
+  stamp(p.dbg, p.dbg && it.head == 0 && it.tile == 0 && tid == 0, 2, kTlIters - 2, 7);   // kernel entry
   if (tid == 0) {
     tc05::tma_prefetch_desc(&tmq); tc05::tma_prefetch_desc(&tmk); tc05::tma_prefetch_desc(&tmv);
     tc05::tma_prefetch_desc(&tmo);
     mbar_init(bar_q, 1);
+    mbar_init(bar_qe, 1);
+    mbar_init(bar_stg, 1);
     for (int s = 0; s < 2; ++s) {
       mbar_init(bar_kf + 8 * s, kPaged ? kPfPageThreads : 1); mbar_init(bar_ke + 8 * s, 1);
       mbar_init(bar_vf + 8 * s, kPaged ? kPfPageThreads : 1); mbar_init(bar_ve + 8 * s, 1);
       mbar_init(bar_s + 8 * s, 1); mbar_init(bar_p + 8 * s, 128); mbar_init(bar_o + 8 * s, 1);
       mbar_init(bar_ph + 8 * s, 128);
+      mbar_init(bar_cf + 8 * s, 1); mbar_init(bar_ce + 8 * s, kClcReaders);
     }
     asm volatile("st.shared.f32 [%0], %1;" :: "r"(sc_slot), "f"(p.scale_log2) : "memory");
     mbar_init_fence();
@@ -198,25 +243,18 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant
     // fence after its barrier wait.
     asm volatile("setmaxnreg.dec.sync.aligned.u32 56;");
     const int pt = (warp == 8 ? 0 : warp - 9) * 32 + lane;          // 0 .. 95
-    if (pt == 0) {
-      mbar_expect_tx(bar_q, (nB ? 2 : 1) * kTileBytes);
-#pragma unroll
-      for (int a = 0; a < kAtoms; ++a) tc05::tma_load_3d(sQ + a * kAtomBytes, &tmq, a * 64, head, qtok0 + q0, bar_q);
-      if (nB) {
-#pragma unroll
-        for (int a = 0; a < kAtoms; ++a)
-          tc05::tma_load_3d(sQ + kTileBytes + a * kAtomBytes, &tmq, a * 64, head, qtok0 + q0 + 128, bar_q);
-      }
-    }
     const int shB = p.block_shift, B = 1 << shB;
     const int D = p.head_size;
     const int64_t page_bytes = static_cast<int64_t>(D) * B * 2;
-    const int64_t block_stride = page_bytes * p.num_heads, head_off = page_bytes * head;
-    const int32_t* table = p.block_tables + static_cast<int64_t>(ktok0) * p.max_blocks;   // ktok0 = sequence index
+    const int64_t block_stride = page_bytes * p.num_heads;
     const char* kc = static_cast<const char*>(p.key_cache);
     const char* vc = static_cast<const char*>(p.value_cache);
     const int npg = kPfCols >> shB;                 // pages per 128-token tile
     const int kchunks = (D >> 3) << shB;            // 16-byte chunks of a K page, of a V page likewise
+    const int iters = (kchunks + kPfPageThreads - 1) / kPfPageThreads;
+    int64_t head_off = 0;
+    const int32_t* table = nullptr;
+    int klen = 0;
     // block numbers of a tile's pages: lane l fetches page l's (one coalesced load per warp, issued a tile ahead
     // so its latency hides behind the copies of the current tile), the page loops read them by shuffle
     auto tile_blocks = [&](int t) {
@@ -226,7 +264,6 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant
     // The producer warps share their schedulers with the softmax warps, so instructions per copy are what
     // counts: everything that does not depend on the page (the chunk's place in the page, its swizzled place
     // in the tile) is computed once per thread-chunk, the page loop inside adds the page's base and copies.
-    const int iters = (kchunks + kPfPageThreads - 1) / kPfPageThreads;
     auto load_k = [&](int t, uint32_t dst, int blocks) {
       const int nvalid = klen - t * kPfCols;        // tokens of this tile inside the context
       for (int i = 0; i < iters; ++i) {
@@ -265,18 +302,38 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant
         }
       }
     };
-    int next_blocks = tile_blocks(0);
-    for (int j = 0; j < nmax; ++j) {
-      const int s = j & 1;
-      const uint32_t ph = ((j >> 1) & 1) ^ 1;
-      const int blocks = next_blocks;
-      if (j + 1 < nmax) next_blocks = tile_blocks(j + 1);
-      mbar_wait(bar_ke + 8 * s, ph);
-      load_k(j, sK + s * kTileBytes, blocks);
-      cp_async_arrive(bar_kf + 8 * s);              // arrives by itself once this thread's copies have landed
-      mbar_wait(bar_ve + 8 * s, ph);
-      load_v(j, sV + s * kTileBytes, blocks);
-      cp_async_arrive(bar_vf + 8 * s);
+    int g = 0;                                      // K/V tiles loaded so far: the rings run on across items
+    for (int n = 0;; ++n) {
+      if (pt == 0) {
+        request_next(n);
+        if (n > 0) mbar_wait(bar_qe, (n - 1) & 1);  // the previous item's last Q.K^T has read the Q tiles
+        mbar_expect_tx(bar_q, (it.nB ? 2 : 1) * kTileBytes);
+#pragma unroll
+        for (int a = 0; a < kAtoms; ++a)
+          tc05::tma_load_3d(sQ + a * kAtomBytes, &tmq, a * 64, it.head, it.qtok0 + it.q0, bar_q);
+        if (it.nB) {
+#pragma unroll
+          for (int a = 0; a < kAtoms; ++a)
+            tc05::tma_load_3d(sQ + kTileBytes + a * kAtomBytes, &tmq, a * 64, it.head, it.qtok0 + it.q0 + 128, bar_q);
+        }
+      }
+      head_off = page_bytes * it.head;
+      table = p.block_tables + static_cast<int64_t>(it.ktok0) * p.max_blocks;   // ktok0 = sequence index
+      klen = it.klen;
+      int next_blocks = tile_blocks(0);
+      for (int j = 0; j < it.nmax; ++j, ++g) {
+        const int s = g & 1;
+        const uint32_t ph = ((g >> 1) & 1) ^ 1;     // first use of a stage passes immediately
+        const int blocks = next_blocks;
+        if (j + 1 < it.nmax) next_blocks = tile_blocks(j + 1);
+        mbar_wait(bar_ke + 8 * s, ph);
+        load_k(j, sK + s * kTileBytes, blocks);
+        cp_async_arrive(bar_kf + 8 * s);            // arrives by itself once this thread's copies have landed
+        mbar_wait(bar_ve + 8 * s, ph);
+        load_v(j, sV + s * kTileBytes, blocks);
+        cp_async_arrive(bar_vf + 8 * s);
+      }
+      if (!next_item(n, it, true)) break;
     }
     asm volatile("cp.async.wait_all;" ::: "memory");   // nothing of this thread's may be in flight when the CTA exits
   } else if (warp == 8) {
@@ -285,20 +342,26 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant
     if (lane == 0) {
       auto load_tile = [&](const CUtensorMap* map, uint32_t dst, int row0, uint32_t bar) {
 #pragma unroll
-        for (int a = 0; a < kAtoms; ++a) tc05::tma_load_3d(dst + a * kAtomBytes, map, a * 64, head, row0, bar);
+        for (int a = 0; a < kAtoms; ++a) tc05::tma_load_3d(dst + a * kAtomBytes, map, a * 64, it.head, row0, bar);
       };
-      mbar_expect_tx(bar_q, (nB ? 2 : 1) * kTileBytes);
-      load_tile(&tmq, sQ, qtok0 + q0, bar_q);
-      if (nB) load_tile(&tmq, sQ + kTileBytes, qtok0 + q0 + 128, bar_q);
-      for (int j = 0; j < nmax; ++j) {
-        const int s = j & 1;
-        const uint32_t ph = ((j >> 1) & 1) ^ 1;    // first use of a stage passes immediately
-        mbar_wait(bar_ke + 8 * s, ph);
-        mbar_expect_tx(bar_kf + 8 * s, kTileBytes);
-        load_tile(&tmk, sK + s * kTileBytes, ktok0 + j * kPfCols, bar_kf + 8 * s);
-        mbar_wait(bar_ve + 8 * s, ph);
-        mbar_expect_tx(bar_vf + 8 * s, kTileBytes);
-        load_tile(&tmv, sV + s * kTileBytes, ktok0 + j * kPfCols, bar_vf + 8 * s);
+      int g = 0;                                    // K/V tiles loaded so far: the rings run on across items
+      for (int n = 0;; ++n) {
+        request_next(n);
+        if (n > 0) mbar_wait(bar_qe, (n - 1) & 1);  // the previous item's last Q.K^T has read the Q tiles
+        mbar_expect_tx(bar_q, (it.nB ? 2 : 1) * kTileBytes);
+        load_tile(&tmq, sQ, it.qtok0 + it.q0, bar_q);
+        if (it.nB) load_tile(&tmq, sQ + kTileBytes, it.qtok0 + it.q0 + 128, bar_q);
+        for (int j = 0; j < it.nmax; ++j, ++g) {
+          const int s = g & 1;
+          const uint32_t ph = ((g >> 1) & 1) ^ 1;  // first use of a stage passes immediately
+          mbar_wait(bar_ke + 8 * s, ph);
+          mbar_expect_tx(bar_kf + 8 * s, kTileBytes);
+          load_tile(&tmk, sK + s * kTileBytes, it.ktok0 + j * kPfCols, bar_kf + 8 * s);
+          mbar_wait(bar_ve + 8 * s, ph);
+          mbar_expect_tx(bar_vf + 8 * s, kTileBytes);
+          load_tile(&tmv, sV + s * kTileBytes, it.ktok0 + j * kPfCols, bar_vf + 8 * s);
+        }
+        if (!next_item(n, it, true)) break;
       }
     }
   } else if (warp == 9) {
@@ -308,12 +371,11 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant
     // Descriptors: one 32-bit add on the low word of a per-tile base (the start-address field, bytes >> 4).
     const bool leader = tc05::elect_one();
     const uint32_t tm = __shfl_sync(0xffffffffu, tmem, 0);
-    const bool tl = p.dbg && head == 0 && tile == 0 && lane == 0;
     auto desc = [](uint64_t base, uint32_t byte_off) { return base + (byte_off >> 4); };
     const uint64_t dq = tc05::smem_desc_sw128(sQ, 16, 1024), dk = tc05::smem_desc_sw128(sK, 16, 1024);
     const uint64_t dv = kPaged ? tc05::smem_desc_sw128(sV, 16, 1024) : tc05::smem_desc_sw128(sV, kAtomBytes, 1024);
-    auto issue_qk = [&](int i, int j) {             // S_i = Q_i . K_j^T
-      const uint64_t qb = desc(dq, i * kTileBytes), kb = desc(dk, (j & 1) * kTileBytes);
+    auto issue_qk = [&](int i, int g) {             // S_i = Q_i . K^T, K in ring slot g
+      const uint64_t qb = desc(dq, i * kTileBytes), kb = desc(dk, (g & 1) * kTileBytes);
 #pragma unroll
       for (int kk = 0; kk < DP / 16; ++kk) {
         if (kk >= qk_steps) break;
@@ -321,60 +383,73 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant
         tc05::mma_ss_w(leader, tm + kTmS + 128 * i, desc(qb, off), desc(kb, off), kIdescQK, kk > 0);
       }
     };
-    auto issue_pv = [&](int i, int j, int half) {   // O_i (+)= P_i . V_j, keys 64 half .. 64 half + 63 of the tile
-      const uint64_t vb = desc(dv, (j & 1) * kTileBytes);
+    auto issue_pv = [&](int i, int g, bool first, int half) {   // O_i (+)= P_i . V, keys 64 half .. 64 half + 63 of the tile
+      const uint64_t vb = desc(dv, (g & 1) * kTileBytes);
 #pragma unroll
       for (int kk = half * (kPfCols / 32); kk < (half + 1) * (kPfCols / 32); ++kk) {
         const uint32_t off = kPaged ? (kk >> 2) * kVAtomBytes + (kk & 3) * 32 : kk * 2048;
-        tc05::mma_ts_w(leader, tm + kTmO + 128 * i, tm + kTmS + 128 * i + kk * 8, desc(vb, off), idesc_pv, j > 0 || kk > 0);
+        tc05::mma_ts_w(leader, tm + kTmO + 128 * i, tm + kTmS + 128 * i + kk * 8, desc(vb, off), idesc_pv, !first || kk > 0);
       }
     };
-    mbar_wait(bar_q, 0);
-    mbar_wait(bar_kf, 0);
-    stamp(p.dbg, tl, 2, 0, 6);
-    if (kPaged) tc05::fence_async_smem();           // cp.async wrote through the generic proxy
-    tc05::fence_after_sync();
-    issue_qk(0, 0);
-    tc05::mma_commit_w(leader, bar_s);
-    if (nB) { issue_qk(1, 0); tc05::mma_commit_w(leader, bar_s + 8); }
-    tc05::mma_commit_w(leader, bar_ke);             // K_0 is free once these have run
-    for (int j = 0; j < nmax; ++j) {
-      const int s = j & 1;
-      const bool more_k = j + 1 < nmax;
-      mbar_wait(bar_vf + 8 * s, (j >> 1) & 1);
-      if (kPaged) tc05::fence_async_smem();
-      stamp(p.dbg, tl, 2, j, 4);
+    int g0 = 0;                                     // ring slot of this item's K_0 / V_0
+    int cs[2] = {0, 0};                             // S tiles of A / B so far: the phases of bar_s, bar_p, bar_ph
+    for (int n = 0;; ++n) {
+      const bool tl = p.dbg && it.head == 0 && it.tile == 0 && lane == 0;
+      const int nA = it.nA, nB = it.nB, nmax = it.nmax;
+      mbar_wait(bar_q, n & 1);
+      mbar_wait(bar_kf + 8 * (g0 & 1), (g0 >> 1) & 1);
+      stamp(p.dbg, tl, 2, 0, 6);
+      if (kPaged) tc05::fence_async_smem();         // cp.async wrote through the generic proxy
+      tc05::fence_after_sync();
+      issue_qk(0, g0);
+      tc05::mma_commit_w(leader, bar_s);
+      if (nB) { issue_qk(1, g0); tc05::mma_commit_w(leader, bar_s + 8); }
+      tc05::mma_commit_w(leader, bar_ke + 8 * (g0 & 1));   // K_0 is free once these have run
+      if (nmax == 1) tc05::mma_commit_w(leader, bar_qe);
+      for (int j = 0; j < nmax; ++j) {
+        const int g = g0 + j, s = g & 1;
+        const bool more_k = j + 1 < nmax;
+        mbar_wait(bar_vf + 8 * s, (g >> 1) & 1);
+        if (kPaged) tc05::fence_async_smem();
+        stamp(p.dbg, tl, 2, j, 4);
 #pragma unroll
-      for (int i = 0; i < 2; ++i) {
-        const int ni = i ? nB : nA;
-        if (j < ni) {
-          // P_i of tile j arrives in two halves: the first half's product runs while the softmax group is
-          // still in the exponentials of the second
-          if (!(p.free_run & 1)) mbar_wait(bar_ph + 8 * i, j & 1);
-          tc05::fence_after_sync();
-          stamp(p.dbg, tl, 2, j, 2 * i);
-          issue_pv(i, j, 0);
-          if (!(p.free_run & 1)) mbar_wait(bar_p + 8 * i, j & 1);
-          tc05::fence_after_sync();
-          issue_pv(i, j, 1);
-          if (j + 1 < ni) {
-            if (i == 0 || j + 1 >= nA) {            // K_{j+1} is needed from here on, not before the P.V above
-              mbar_wait(bar_kf + 8 * (s ^ 1), ((j + 1) >> 1) & 1);
-              if (kPaged) tc05::fence_async_smem();
+        for (int i = 0; i < 2; ++i) {
+          const int ni = i ? nB : nA;
+          if (j < ni) {
+            // P_i of tile j arrives in two halves: the first half's product runs while the softmax group is
+            // still in the exponentials of the second
+            const uint32_t php = (cs[i] + j) & 1;
+            mbar_wait(bar_ph + 8 * i, php);
+            tc05::fence_after_sync();
+            stamp(p.dbg, tl, 2, j, 2 * i);
+            issue_pv(i, g, j == 0, 0);
+            mbar_wait(bar_p + 8 * i, php);
+            tc05::fence_after_sync();
+            issue_pv(i, g, false, 1);
+            if (j + 1 < ni) {
+              if (i == 0 || j + 1 >= nA) {          // K_{j+1} is needed from here on, not before the P.V above
+                mbar_wait(bar_kf + 8 * (s ^ 1), ((g + 1) >> 1) & 1);
+                if (kPaged) tc05::fence_async_smem();
+              }
+              issue_qk(i, g + 1);
+              tc05::mma_commit_w(leader, bar_s + 8 * i);
+            } else {
+              tc05::mma_commit_w(leader, bar_o + 8 * i);
             }
-            issue_qk(i, j + 1);
-            tc05::mma_commit_w(leader, bar_s + 8 * i);
-          } else {
-            tc05::mma_commit_w(leader, bar_o + 8 * i);
+            stamp(p.dbg, tl, 2, j, 2 * i + 1);
           }
-          stamp(p.dbg, tl, 2, j, 2 * i + 1);
         }
+        tc05::mma_commit_w(leader, bar_ve + 8 * s);   // V_j and K_{j+1} are consumed by everything issued so far
+        if (more_k) tc05::mma_commit_w(leader, bar_ke + 8 * (s ^ 1));
+        if (j + 2 == nmax) tc05::mma_commit_w(leader, bar_qe);   // the item's last Q.K^T is among them
       }
-      tc05::mma_commit_w(leader, bar_ve + 8 * s);   // V_j and K_{j+1} are consumed by everything issued so far
-      if (more_k) tc05::mma_commit_w(leader, bar_ke + 8 * (s ^ 1));
+      g0 += nmax;
+      cs[0] += nA;
+      cs[1] += nB;
+      if (!next_item(n, it, lane == 0)) break;
     }
-    // the last commit must have landed in this CTA's shared memory before the CTA may exit
-    mbar_wait(bar_ve + 8 * ((nmax - 1) & 1), ((nmax - 1) >> 1) & 1);
+    // the last commits must have landed in this CTA's shared memory before the CTA may exit
+    mbar_wait(bar_ve + 8 * ((g0 - 1) & 1), ((g0 - 1) >> 1) & 1);
   } else if (warp >= 10) {
     // register donors.  384 threads x 168 registers is the CTA's pool = 128 x 56 + 256 x 224; setmaxnreg must be
     // the same instruction in all four warps of a warpgroup (warps 8-11), whatever branch they sit in
@@ -383,183 +458,195 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant
     // ===================== softmax groups =====================
     asm volatile("setmaxnreg.inc.sync.aligned.u32 224;");
     const int grp = warp >> 2;                      // 0: tile A, 1: tile B
-    const int ni = grp ? nB : nA;
     const int r = tid & 127;                        // row inside the tile
-    const int qi0 = q0 + 128 * grp;                 // first row of this tile inside the prompt
     const uint32_t lane_base = tmem + (static_cast<uint32_t>((warp & 3) * 32) << 16);
     const uint32_t tS = lane_base + kTmS + 128 * grp, tO = lane_base + kTmO + 128 * grp;
-    const bool dump = p.dbg && head == 0 && tile == 0 && grp == 0 && !(p.free_run & 4);   // 4: stamps only
-    const bool tl = p.dbg && head == 0 && tile == 0 && r == 0;
-    float m_run = -CUDART_INF_F, l_run = 0.f;
-    // The exponentials of a tile keep the SM's special-function unit busy for as long as the tensor core
-    // needs for that tile's two matrix products.  Left alone, the two groups drift into phase -- both in
-    // their exponentials (sharing the unit), then both waiting for the tensor core -- and each unit idles
-    // half of the time.  So the exponential section is a critical section that alternates A, B, A, B, ...:
-    // while one group is in it the tensor core runs the other tile's P.V and next Q.K^T.
-    const bool pingpong = nB > 0 && !(p.free_run & 2);
     const int bar_mine = 1 + grp, bar_other = 2 - grp;
-    if (pingpong && grp == 1) named_arrive(bar_other);          // A goes first
-    for (int j = 0; j < ((p.free_run & 1) ? 0 : ni); ++j) {
-      stamp(p.dbg, tl, grp, j, 0);
-      mbar_wait(bar_s + 8 * grp, j & 1);
-      tc05::fence_after_sync();
-      stamp(p.dbg, tl, grp, j, 1);
-      uint32_t s[4][32];
+    int cs = 0, co = 0;                             // S tiles / finished tiles of this group so far (barrier phases)
+    for (int n = 0;; ++n) {
+      const int nA = it.nA, nB = it.nB;
+      const int ni = grp ? nB : nA;
+      const int head = it.head, qtok0 = it.qtok0, qlen = it.qlen, klen = it.klen, koff = it.koff;
+      const int qi0 = it.q0 + 128 * grp;            // first row of this tile inside the prompt
+      const bool dump = p.dbg && head == 0 && it.tile == 0 && grp == 0;
+      const bool tl = p.dbg && head == 0 && it.tile == 0 && r == 0;
+      float m_run = -CUDART_INF_F, l_run = 0.f;
+      // The exponentials of a tile keep the SM's special-function unit busy for as long as the tensor core
+      // needs for that tile's two matrix products.  Left alone, the two groups drift into phase -- both in
+      // their exponentials (sharing the unit), then both waiting for the tensor core -- and each unit idles
+      // half of the time.  So the exponential section is a critical section that alternates A, B, A, B, ...:
+      // while one group is in it the tensor core runs the other tile's P.V and next Q.K^T.
+      const bool pingpong = nB > 0;
+      if (pingpong && grp == 1) named_arrive(bar_other);          // A goes first
+      for (int j = 0; j < ni; ++j) {
+        stamp(p.dbg, tl, grp, j, 0);
+        mbar_wait(bar_s + 8 * grp, (cs + j) & 1);
+        tc05::fence_after_sync();
+        stamp(p.dbg, tl, grp, j, 1);
+        uint32_t s[4][32];
 #pragma unroll
-      for (int c = 0; c < 4; ++c) tc05::tmem_ld32(tS + c * 32, s[c]);
-      tc05::tmem_wait_ld();
-      if (dump && j == 0) {
+        for (int c = 0; c < 4; ++c) tc05::tmem_ld32(tS + c * 32, s[c]);
+        tc05::tmem_wait_ld();
+        if (dump && j == 0) {
 #pragma unroll
-        for (int c = 0; c < 4; ++c)
+          for (int c = 0; c < 4; ++c)
 #pragma unroll
-          for (int i = 0; i < 32; ++i) p.dbg[r * 128 + c * 32 + i] = __uint_as_float(s[c][i]);
-      }
-      // only tiles reaching past the last key of the tile's FIRST row need masking: the diagonal tile of a
-      // plain prompt, at most the last two tiles when cached keys shift the diagonal off the tile grid.
-      // A row wholly masked in such a tile (never tile 0) keeps its running maximum: all its p are 0.
-      if ((j + 1) * kPfCols - 1 > min(qi0 + koff, klen - 1)) {
-        const int lim = min(qi0 + r + koff, klen - 1) - j * kPfCols;   // last valid column of this row
+            for (int i = 0; i < 32; ++i) p.dbg[r * 128 + c * 32 + i] = __uint_as_float(s[c][i]);
+        }
+        // only tiles reaching past the last key of the tile's FIRST row need masking: the diagonal tile of a
+        // plain prompt, at most the last two tiles when cached keys shift the diagonal off the tile grid.
+        // A row wholly masked in such a tile (never tile 0) keeps its running maximum: all its p are 0.
+        if ((j + 1) * kPfCols - 1 > min(qi0 + koff, klen - 1)) {
+          const int lim = min(qi0 + r + koff, klen - 1) - j * kPfCols;   // last valid column of this row
 #pragma unroll
-        for (int c = 0; c < 4; ++c)
+          for (int c = 0; c < 4; ++c)
 #pragma unroll
-          for (int i = 0; i < 32; ++i)
-            if (c * 32 + i > lim) s[c][i] = 0xff800000u;   // -inf
-      }
-      // row maximum of the raw logits (scale > 0), four independent chains of 3-input max
-      float mx[4];
+            for (int i = 0; i < 32; ++i)
+              if (c * 32 + i > lim) s[c][i] = 0xff800000u;   // -inf
+        }
+        // row maximum of the raw logits (scale > 0), four independent chains of 3-input max
+        float mx[4];
 #pragma unroll
-      for (int c = 0; c < 4; ++c) {
-        mx[c] = max3(__uint_as_float(s[c][0]), __uint_as_float(s[c][1]), __uint_as_float(s[c][2]));
+        for (int c = 0; c < 4; ++c) {
+          mx[c] = max3(__uint_as_float(s[c][0]), __uint_as_float(s[c][1]), __uint_as_float(s[c][2]));
 #pragma unroll
-        for (int i = 3; i + 1 < 32; i += 2) mx[c] = max3(mx[c], __uint_as_float(s[c][i]), __uint_as_float(s[c][i + 1]));
-        mx[c] = fmaxf(mx[c], __uint_as_float(s[c][31]));
-      }
-      const float m_tile = fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3])) * p.scale_log2;
-      // Lazy rescaling: the reference maximum only moves when the row maximum grew by more than 2^8; until then
-      // probabilities may exceed 1 (by at most 2^8), which fp32 sums and 16-bit P hold without loss, and
-      // O / l is unchanged because both carry the same reference.  O_i is quiescent here: S_j ready implies
-      // the previous P.V of this tile completed (in-order tensor pipe).
-      const bool move = m_tile > m_run + 8.f;       // always true on the first tile (m_run = -inf)
-      if (__any_sync(0xffffffffu, move)) {
-        const float alpha = move ? ex2(m_run - m_tile) : 1.f;
-        if (move) { m_run = m_tile; l_run *= alpha; }
-        if (j > 0) {
+          for (int i = 3; i + 1 < 32; i += 2) mx[c] = max3(mx[c], __uint_as_float(s[c][i]), __uint_as_float(s[c][i + 1]));
+          mx[c] = fmaxf(mx[c], __uint_as_float(s[c][31]));
+        }
+        const float m_tile = fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3])) * p.scale_log2;
+        // Lazy rescaling: the reference maximum only moves when the row maximum grew by more than 2^8; until then
+        // probabilities may exceed 1 (by at most 2^8), which fp32 sums and 16-bit P hold without loss, and
+        // O / l is unchanged because both carry the same reference.  O_i is quiescent here: S_j ready implies
+        // the previous P.V of this tile completed (in-order tensor pipe).
+        const bool move = m_tile > m_run + 8.f;     // always true on the first tile (m_run = -inf)
+        if (__any_sync(0xffffffffu, move)) {
+          const float alpha = move ? ex2(m_run - m_tile) : 1.f;
+          if (move) { m_run = m_tile; l_run *= alpha; }
+          if (j > 0) {
 #pragma unroll
-          for (int c = 0; c < DP / 32; ++c) {
-            uint32_t o[32];
-            tc05::tmem_ld32(tO + c * 32, o);
-            tc05::tmem_wait_ld();
+            for (int c = 0; c < DP / 32; ++c) {
+              uint32_t o[32];
+              tc05::tmem_ld32(tO + c * 32, o);
+              tc05::tmem_wait_ld();
 #pragma unroll
-            for (int i = 0; i < 32; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
-            tc05::tmem_st32(tO + c * 32, o);
+              for (int i = 0; i < 32; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
+              tc05::tmem_st32(tO + c * 32, o);
+            }
           }
         }
-      }
-      const float neg_m = -m_run;
-      float sum[4] = {0.f, 0.f, 0.f, 0.f};
-      stamp(p.dbg, tl, grp, j, 2);
-      if (pingpong && j < nA) named_sync(bar_mine);   // B's extra (diagonal) tile runs after A's last: no turn to wait for
-      // ptxas moves arithmetic (and MUFU) across BAR.SYNC freely; what it cannot move is a value loaded
-      // after the barrier, so the section's multiplier is re-read from shared memory here
-      float sc;
-      asm volatile("ld.volatile.shared.f32 %0, [%1];" : "=f"(sc) : "r"(sc_slot) : "memory");
-      stamp(p.dbg, tl, grp, j, 3);
+        const float neg_m = -m_run;
+        float sum[4] = {0.f, 0.f, 0.f, 0.f};
+        stamp(p.dbg, tl, grp, j, 2);
+        if (pingpong && j < nA) named_sync(bar_mine);   // B's extra (diagonal) tile runs after A's last: no turn to wait for
+        // ptxas moves arithmetic (and MUFU) across BAR.SYNC freely; what it cannot move is a value loaded
+        // after the barrier, so the section's multiplier is re-read from shared memory here
+        float sc;
+        asm volatile("ld.volatile.shared.f32 %0, [%1];" : "=f"(sc) : "r"(sc_slot) : "memory");
+        stamp(p.dbg, tl, grp, j, 3);
 #pragma unroll
-      for (int c2 = 0; c2 < 2; ++c2) {
-        uint32_t pk[32];
+        for (int c2 = 0; c2 < 2; ++c2) {
+          uint32_t pk[32];
 #pragma unroll
-        for (int h = 0; h < 2; ++h)
+          for (int h = 0; h < 2; ++h)
 #pragma unroll
-          for (int i = 0; i < 32; i += 2) {
-            float a0, a1;
-            ffma2(a0, a1, __uint_as_float(s[c2 * 2 + h][i]), __uint_as_float(s[c2 * 2 + h][i + 1]), sc, neg_m);
-            const float p0 = ex2_pinned(a0), p1 = ex2_pinned(a1);
-            fadd2(sum[(i >> 1) & 1 ? 2 : 0], sum[(i >> 1) & 1 ? 3 : 1], p0, p1);
-            pk[h * 16 + (i >> 1)] = pack2<T>(p0, p1);
+            for (int i = 0; i < 32; i += 2) {
+              float a0, a1;
+              ffma2(a0, a1, __uint_as_float(s[c2 * 2 + h][i]), __uint_as_float(s[c2 * 2 + h][i + 1]), sc, neg_m);
+              const float p0 = ex2_pinned(a0), p1 = ex2_pinned(a1);
+              fadd2(sum[(i >> 1) & 1 ? 2 : 0], sum[(i >> 1) & 1 ? 3 : 1], p0, p1);
+              pk[h * 16 + (i >> 1)] = pack2<T>(p0, p1);
+            }
+          tc05::tmem_st32(tS + c2 * 32, pk);
+          if (c2 == 0) {                              // keys 0-63 of P: the issuer starts P.V on them
+            tc05::tmem_wait_st();
+            tc05::fence_before_sync();
+            mbar_arrive(bar_ph + 8 * grp);
+            stamp(p.dbg, tl, grp, j, 7);
           }
-        tc05::tmem_st32(tS + c2 * 32, pk);
-        if (c2 == 0) {                                // keys 0-63 of P: the issuer starts P.V on them
-          tc05::tmem_wait_st();
-          tc05::fence_before_sync();
-          mbar_arrive(bar_ph + 8 * grp);
-          stamp(p.dbg, tl, grp, j, 7);
         }
+        stamp(p.dbg, tl, grp, j, 4);
+        // hand over: B after its tile j lets A into tile j + 1 (if A has one); A after tile j lets B into tile j.
+        // Every arrive is matched by exactly one later sync of the other group before the next arrive on the same
+        // barrier can happen (two back-to-back arrives would complete the barrier with nobody waiting); the
+        // counts balance within an item (A syncs nA times: B's opening arrive + nA - 1; B syncs nA times).
+        if (pingpong && (grp == 0 || j + 1 < nA)) named_arrive(bar_other);
+        l_run += (sum[0] + sum[1]) + (sum[2] + sum[3]);
+        tc05::tmem_wait_st();
+        tc05::fence_before_sync();
+        mbar_arrive(bar_p + 8 * grp);
+        stamp(p.dbg, tl, grp, j, 5);
       }
-      stamp(p.dbg, tl, grp, j, 4);
-      // hand over: B after its tile j lets A into tile j + 1 (if A has one); A after tile j lets B into tile j.
-      // Every arrive is matched by exactly one later sync of the other group before the next arrive on the same
-      // barrier can happen (two back-to-back arrives would complete the barrier with nobody waiting).
-      if (pingpong && (grp == 0 || j + 1 < nA)) named_arrive(bar_other);
-      l_run += (sum[0] + sum[1]) + (sum[2] + sum[3]);
-      tc05::tmem_wait_st();
-      tc05::fence_before_sync();
-      mbar_arrive(bar_p + 8 * grp);
-      stamp(p.dbg, tl, grp, j, 5);
-    }
-    if (ni > 0) {
+      cs += ni;
       // ---- epilogue: O / l -> out ---------------------------------------------------------
-      stamp(p.dbg, tl, grp, kTlIters - 1, 0);
-      mbar_wait(bar_o + 8 * grp, 0);
-      tc05::fence_after_sync();
-      stamp(p.dbg, tl, grp, kTlIters - 1, 1);
       // Every thread holds one row of O; stored from here, a warp's 16-byte stores would land in 32 different
       // rows (32 wavefronts per instruction: measured 4400 clk for the tile).  So the tile is staged in shared
-      // memory -- the Q tile's slot, free since this tile's last Q.K^T, in the same 128-byte-swizzled layout --
-      // and leaves as one TMA store per 64-column group; a prompt's last, partial tile (rows past the prompt
-      // belong to the next one) leaves as row-contiguous 16-byte stores of its valid rows instead.
-      const int D = p.head_size;
-      const float inv = 1.f / l_run;
-      const uint32_t stg = sQ + grp * kTileBytes;
+      // memory in the 128-byte-swizzled layout and leaves as one TMA store per 64-column group; a prompt's last,
+      // partial tile (rows past the prompt belong to the next one) leaves as row-contiguous 16-byte stores of
+      // its valid rows instead.  The staging buffer is used in turns, A and B of item 0, A and B of item 1, ...
+      // (use u = 2 n + group waits for the u-th release); a group without a tile only passes the turn on.
+      if (r == 0) mbar_wait(bar_stg, (grp & 1) ^ 1);   // u & 1 == group
+      if (ni > 0) {
+        stamp(p.dbg, tl, grp, kTlIters - 1, 0);
+        mbar_wait(bar_o + 8 * grp, co & 1);
+        ++co;
+        tc05::fence_after_sync();
+        stamp(p.dbg, tl, grp, kTlIters - 1, 1);
+        const int D = p.head_size;
+        const float inv = 1.f / l_run;
+        named_sync_n(3 + grp, 128);                   // row 0's thread has seen the buffer released
 #pragma unroll
-      for (int c = 0; c < DP / 32; ++c) {
-        uint32_t o[32];
-        tc05::tmem_ld32(tO + c * 32, o);
-        tc05::tmem_wait_ld();
-        if (dump) {
+        for (int c = 0; c < DP / 32; ++c) {
+          uint32_t o[32];
+          tc05::tmem_ld32(tO + c * 32, o);
+          tc05::tmem_wait_ld();
+          if (dump) {
 #pragma unroll
-          for (int i = 0; i < 32; ++i) p.dbg[128 * 128 + r * DP + c * 32 + i] = __uint_as_float(o[i]);
-          if (c == 0) { p.dbg[128 * 128 + 128 * DP + r] = l_run; p.dbg[128 * 128 + 128 * DP + 128 + r] = m_run; }
+            for (int i = 0; i < 32; ++i) p.dbg[128 * 128 + r * DP + c * 32 + i] = __uint_as_float(o[i]);
+            if (c == 0) { p.dbg[128 * 128 + 128 * DP + r] = l_run; p.dbg[128 * 128 + 128 * DP + 128 + r] = m_run; }
+          }
+#pragma unroll
+          for (int v = 0; v < 4; ++v) {               // 8 elements = one 16-byte chunk
+            const uint32_t w0 = pack2<T>(__uint_as_float(o[v * 8 + 0]) * inv, __uint_as_float(o[v * 8 + 1]) * inv);
+            const uint32_t w1 = pack2<T>(__uint_as_float(o[v * 8 + 2]) * inv, __uint_as_float(o[v * 8 + 3]) * inv);
+            const uint32_t w2 = pack2<T>(__uint_as_float(o[v * 8 + 4]) * inv, __uint_as_float(o[v * 8 + 5]) * inv);
+            const uint32_t w3 = pack2<T>(__uint_as_float(o[v * 8 + 6]) * inv, __uint_as_float(o[v * 8 + 7]) * inv);
+            const uint32_t chunk = (c & 1) * 4 + v;
+            const uint32_t dst = sStg + (c >> 1) * kAtomBytes + r * 128 + ((chunk ^ (r & 7)) << 4);
+            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" :: "r"(dst), "r"(w0), "r"(w1), "r"(w2), "r"(w3) : "memory");
+          }
         }
+        const int valid = min(128, qlen - qi0);       // rows of this tile inside the prompt
+        if (valid == 128) {
+          tc05::fence_async_smem();
+          named_sync_n(3 + grp, 128);
+          if (r == 0) {
 #pragma unroll
-        for (int v = 0; v < 4; ++v) {                 // 8 elements = one 16-byte chunk
-          const uint32_t w0 = pack2<T>(__uint_as_float(o[v * 8 + 0]) * inv, __uint_as_float(o[v * 8 + 1]) * inv);
-          const uint32_t w1 = pack2<T>(__uint_as_float(o[v * 8 + 2]) * inv, __uint_as_float(o[v * 8 + 3]) * inv);
-          const uint32_t w2 = pack2<T>(__uint_as_float(o[v * 8 + 4]) * inv, __uint_as_float(o[v * 8 + 5]) * inv);
-          const uint32_t w3 = pack2<T>(__uint_as_float(o[v * 8 + 6]) * inv, __uint_as_float(o[v * 8 + 7]) * inv);
-          const uint32_t chunk = (c & 1) * 4 + v;
-          const uint32_t dst = stg + (c >> 1) * kAtomBytes + r * 128 + ((chunk ^ (r & 7)) << 4);
-          asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" :: "r"(dst), "r"(w0), "r"(w1), "r"(w2), "r"(w3) : "memory");
+            for (int a = 0; a < kAtoms; ++a)
+              if (a * 64 < D) tc05::tma_store_3d(&tmo, sStg + a * kAtomBytes, a * 64, head, qtok0 + qi0);
+            tc05::tma_store_commit();
+            tc05::tma_store_wait_read();
+          }
+        } else {
+          named_sync_n(3 + grp, 128);
+          const int cpr = D / 8;                      // 16-byte chunks per row: 8, 10, 12 or 16
+          char* obase = reinterpret_cast<char*>(p.out) +
+                        ((static_cast<int64_t>(qtok0) + qi0) * p.out_stride + static_cast<int64_t>(head) * D) * 2;
+          for (int idx = r; idx < valid * cpr; idx += 128) {
+            const int row = idx / cpr, chunk = idx - row * cpr;
+            const uint32_t src = sStg + (chunk >> 3) * kAtomBytes + row * 128 + (((chunk & 7) ^ (row & 7)) << 4);
+            uint4 w;
+            asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(w.x), "=r"(w.y), "=r"(w.z), "=r"(w.w) : "r"(src) : "memory");
+            *reinterpret_cast<uint4*>(obase + static_cast<int64_t>(row) * p.out_stride * 2 + chunk * 16) = w;
+          }
+          named_sync_n(3 + grp, 128);                 // everybody has read its chunks
         }
       }
-      const int valid = min(128, qlen - qi0);         // rows of this tile inside the prompt
-      if (valid == 128) {
-        tc05::fence_async_smem();
-        named_sync_n(3 + grp, 128);
-        if (r == 0) {
-#pragma unroll
-          for (int a = 0; a < kAtoms; ++a)
-            if (a * 64 < D) tc05::tma_store_3d(&tmo, stg + a * kAtomBytes, a * 64, head, qtok0 + qi0);
-          tc05::tma_store_commit();
-          tc05::tma_store_wait_read();
-        }
-      } else {
-        named_sync_n(3 + grp, 128);
-        const int cpr = D / 8;                        // 16-byte chunks per row: 8, 10, 12 or 16
-        char* obase = reinterpret_cast<char*>(p.out) +
-                      ((static_cast<int64_t>(qtok0) + qi0) * p.out_stride + static_cast<int64_t>(head) * D) * 2;
-        for (int idx = r; idx < valid * cpr; idx += 128) {
-          const int row = idx / cpr, chunk = idx - row * cpr;
-          const uint32_t src = stg + (chunk >> 3) * kAtomBytes + row * 128 + (((chunk & 7) ^ (row & 7)) << 4);
-          uint4 w;
-          asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(w.x), "=r"(w.y), "=r"(w.z), "=r"(w.w) : "r"(src) : "memory");
-          *reinterpret_cast<uint4*>(obase + static_cast<int64_t>(row) * p.out_stride * 2 + chunk * 16) = w;
-        }
-      }
+      if (r == 0) mbar_arrive(bar_stg);
+      if (!next_item(n, it, true)) break;
     }
   }
   tc05::fence_before_sync();
   __syncthreads();
-  stamp(p.dbg, p.dbg && head == 0 && tile == 0 && tid == 0, 2, kTlIters - 1, 7);   // all warps done
   if (warp == 0) tc05::tmem_free<kTmCols>(tmem);
 }
 

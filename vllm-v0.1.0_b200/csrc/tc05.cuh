@@ -149,6 +149,26 @@ __device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap* map
       "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
       :: "r"(dst), "l"(reinterpret_cast<uint64_t>(map)), "r"(bar), "r"(c0), "r"(c1), "r"(c2) : "memory");
 }
+// Cluster launch control: a running CTA asks the hardware scheduler for the next CTA of the grid that has not
+// started yet.  16-byte answer in shared memory, completion (16 bytes) counted on `bar`.  Canceled = that CTA will
+// never be launched and its blockIdx is ours to work on; not canceled = the grid has no pending CTAs left.
+__device__ __forceinline__ void clc_try_cancel(uint32_t result, uint32_t bar) {
+  asm volatile("clusterlaunchcontrol.try_cancel.async.shared::cta.mbarrier::complete_tx::bytes.b128 [%0], [%1];"
+               :: "r"(result), "r"(bar) : "memory");
+}
+__device__ __forceinline__ bool clc_read(uint32_t result, int& x, int& y) {
+  uint32_t ok, bx = 0, by = 0, bz = 0;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t.reg .b128 r;\n\t"
+      "ld.shared.b128 r, [%4];\n\t"
+      "clusterlaunchcontrol.query_cancel.is_canceled.pred.b128 p, r;\n\t"
+      "selp.u32 %3, 1, 0, p;\n\t"
+      "@p clusterlaunchcontrol.query_cancel.get_first_ctaid.v4.b32.b128 {%0, %1, %2, _}, r;\n\t}"
+      : "+r"(bx), "+r"(by), "+r"(bz), "=r"(ok) : "r"(result) : "memory");
+  x = static_cast<int>(bx);
+  y = static_cast<int>(by);
+  return ok != 0;
+}
 // this CTA's shared memory -> global through a tensor map (bulk async-group completion); the writer must have
 // made its shared-memory stores visible to the async proxy (fence_async_smem) before the issue
 __device__ __forceinline__ void tma_store_3d(const CUtensorMap* map, uint32_t src, int c0, int c1, int c2) {
