@@ -151,11 +151,11 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant
   const uint32_t sV = sK + 2 * kTileBytes;         // two stages
   const uint32_t sStg = sV + 2 * kTileBytes;       // output tile on its way out (one group at a time)
   const uint32_t sBar = sStg + kTileBytes;
-  const uint32_t bar_q = sBar;                     // Q tiles landed
+  const uint32_t bar_q = sBar, bar_q1 = sBar + 224;   // Q_A / Q_B landed
   const uint32_t bar_kf = sBar + 8, bar_ke = sBar + 24, bar_vf = sBar + 40, bar_ve = sBar + 56;   // [2] each
   const uint32_t bar_s = sBar + 72, bar_p = sBar + 88, bar_o = sBar + 104;                        // [2] each
   const uint32_t bar_ph = sBar + 128;              // [2]: the first half of P_i (keys 0-63 of the tile) is in tensor memory
-  const uint32_t bar_qe = sBar + 144;              // the item's last Q.K^T has run: the Q tiles may be overwritten
+  const uint32_t bar_qe = sBar + 144, bar_qe1 = sBar + 232;   // tile A's / B's last Q.K^T of the item has run: Q_i may be overwritten
   const uint32_t bar_stg = sBar + 152;             // the staging buffer's previous user is done with it
   const uint32_t bar_cf = sBar + 160, bar_ce = sBar + 176;   // [2] each: next work item landed / read by everybody
   const uint32_t sClc = sBar + 192;                // [2] x 16 bytes: the scheduler's answers
@@ -204,14 +204,22 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant
     if (ok) it = decode(bx, by);
     return ok;
   };
+  auto peek_item = [&](int n, Item& nx) {          // the same answer, early and without releasing the slot
+    const uint32_t slot = n & 1;
+    mbar_wait(bar_cf + 8 * slot, (n >> 1) & 1);
+    int bx, by;
+    const bool ok = tc05::clc_read(sClc + 16 * slot, bx, by);
+    if (ok) nx = decode(bx, by);
+    return ok;
+  };
   Item it = decode(blockIdx.x, blockIdx.y);
 
   stamp(p.dbg, p.dbg && it.head == 0 && it.tile == 0 && tid == 0, 2, kTlIters - 2, 7);   // kernel entry
   if (tid == 0) {
     tc05::tma_prefetch_desc(&tmq); tc05::tma_prefetch_desc(&tmk); tc05::tma_prefetch_desc(&tmv);
     tc05::tma_prefetch_desc(&tmo);
-    mbar_init(bar_q, 1);
-    mbar_init(bar_qe, 1);
+    mbar_init(bar_q, 1); mbar_init(bar_q1, 1);
+    mbar_init(bar_qe, 1); mbar_init(bar_qe1, 1);
     mbar_init(bar_stg, 1);
     for (int s = 0; s < 2; ++s) {
       mbar_init(bar_kf + 8 * s, kPaged ? kPfPageThreads : 1); mbar_init(bar_ke + 8 * s, 1);
@@ -303,19 +311,15 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant
       }
     };
     int g = 0;                                      // K/V tiles loaded so far: the rings run on across items
+    int cB = 0;                                     // items with a tile B so far (phases of bar_q1 / bar_qe1)
     for (int n = 0;; ++n) {
       if (pt == 0) {
         request_next(n);
-        if (n > 0) mbar_wait(bar_qe, (n - 1) & 1);  // the previous item's last Q.K^T has read the Q tiles
-        mbar_expect_tx(bar_q, (it.nB ? 2 : 1) * kTileBytes);
+        if (n > 0) mbar_wait(bar_qe, (n - 1) & 1);  // the previous item's last Q_A.K^T has read Q_A
+        mbar_expect_tx(bar_q, kTileBytes);
 #pragma unroll
         for (int a = 0; a < kAtoms; ++a)
           tc05::tma_load_3d(sQ + a * kAtomBytes, &tmq, a * 64, it.head, it.qtok0 + it.q0, bar_q);
-        if (it.nB) {
-#pragma unroll
-          for (int a = 0; a < kAtoms; ++a)
-            tc05::tma_load_3d(sQ + kTileBytes + a * kAtomBytes, &tmq, a * 64, it.head, it.qtok0 + it.q0 + 128, bar_q);
-        }
       }
       head_off = page_bytes * it.head;
       table = p.block_tables + static_cast<int64_t>(it.ktok0) * p.max_blocks;   // ktok0 = sequence index
@@ -329,6 +333,14 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant
         mbar_wait(bar_ke + 8 * s, ph);
         load_k(j, sK + s * kTileBytes, blocks);
         cp_async_arrive(bar_kf + 8 * s);            // arrives by itself once this thread's copies have landed
+        if (j == 0 && it.nB && pt == 0) {           // Q_B behind K_0: it is free one iteration later than Q_A
+          if (cB > 0) mbar_wait(bar_qe1, (cB - 1) & 1);
+          mbar_expect_tx(bar_q1, kTileBytes);
+#pragma unroll
+          for (int a = 0; a < kAtoms; ++a)
+            tc05::tma_load_3d(sQ + kTileBytes + a * kAtomBytes, &tmq, a * 64, it.head, it.qtok0 + it.q0 + 128, bar_q1);
+          ++cB;
+        }
         mbar_wait(bar_ve + 8 * s, ph);
         load_v(j, sV + s * kTileBytes, blocks);
         cp_async_arrive(bar_vf + 8 * s);
@@ -345,18 +357,26 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant
         for (int a = 0; a < kAtoms; ++a) tc05::tma_load_3d(dst + a * kAtomBytes, map, a * 64, it.head, row0, bar);
       };
       int g = 0;                                    // K/V tiles loaded so far: the rings run on across items
+      int cB = 0;                                   // items with a tile B so far (phases of bar_q1 / bar_qe1)
       for (int n = 0;; ++n) {
         request_next(n);
-        if (n > 0) mbar_wait(bar_qe, (n - 1) & 1);  // the previous item's last Q.K^T has read the Q tiles
-        mbar_expect_tx(bar_q, (it.nB ? 2 : 1) * kTileBytes);
+        // Q_A is free one iteration before the item ends (A's last Q.K^T), Q_B one later: loaded in that order
+        // with K_0 in between, the next item's first Q_A.K_0^T can run right behind this item's last P_A.V
+        if (n > 0) mbar_wait(bar_qe, (n - 1) & 1);
+        mbar_expect_tx(bar_q, kTileBytes);
         load_tile(&tmq, sQ, it.qtok0 + it.q0, bar_q);
-        if (it.nB) load_tile(&tmq, sQ + kTileBytes, it.qtok0 + it.q0 + 128, bar_q);
         for (int j = 0; j < it.nmax; ++j, ++g) {
           const int s = g & 1;
           const uint32_t ph = ((g >> 1) & 1) ^ 1;  // first use of a stage passes immediately
           mbar_wait(bar_ke + 8 * s, ph);
           mbar_expect_tx(bar_kf + 8 * s, kTileBytes);
           load_tile(&tmk, sK + s * kTileBytes, it.ktok0 + j * kPfCols, bar_kf + 8 * s);
+          if (j == 0 && it.nB) {
+            if (cB > 0) mbar_wait(bar_qe1, (cB - 1) & 1);
+            mbar_expect_tx(bar_q1, kTileBytes);
+            load_tile(&tmq, sQ + kTileBytes, it.qtok0 + it.q0 + 128, bar_q1);
+            ++cB;
+          }
           mbar_wait(bar_ve + 8 * s, ph);
           mbar_expect_tx(bar_vf + 8 * s, kTileBytes);
           load_tile(&tmv, sV + s * kTileBytes, it.ktok0 + j * kPfCols, bar_vf + 8 * s);
@@ -393,25 +413,38 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant
     };
     int g0 = 0;                                     // ring slot of this item's K_0 / V_0
     int cs[2] = {0, 0};                             // S tiles of A / B so far: the phases of bar_s, bar_p, bar_ph
+    int cB = 0;                                     // items with a tile B so far (phase of bar_q1)
+    int started = 0;                                // bit i: S_i of this item's tile 0 was issued during the previous item
+    bool k0_released = false;                       // ... and K_0's stage already handed back behind both of them
     for (int n = 0;; ++n) {
-      const bool tl = p.dbg && it.head == 0 && it.tile == 0 && lane == 0;
+      const bool tl = p.dbg && blockIdx.x == 0 && blockIdx.y == 0 && lane == 0;   // stamps follow CTA 0 through its items
       const int nA = it.nA, nB = it.nB, nmax = it.nmax;
-      mbar_wait(bar_q, n & 1);
-      mbar_wait(bar_kf + 8 * (g0 & 1), (g0 >> 1) & 1);
-      stamp(p.dbg, tl, 2, 0, 6);
-      if (kPaged) tc05::fence_async_smem();         // cp.async wrote through the generic proxy
-      tc05::fence_after_sync();
-      issue_qk(0, g0);
-      tc05::mma_commit_w(leader, bar_s);
-      if (nB) { issue_qk(1, g0); tc05::mma_commit_w(leader, bar_s + 8); }
-      tc05::mma_commit_w(leader, bar_ke + 8 * (g0 & 1));   // K_0 is free once these have run
-      if (nmax == 1) tc05::mma_commit_w(leader, bar_qe);
+      // first Q.K^T of the item, unless the previous item's loop has issued it already (see below)
+      auto first_qk = [&](int i, int item, int cb, int gk) {
+        mbar_wait(i ? bar_q1 : bar_q, (i ? cb : item) & 1);
+        mbar_wait(bar_kf + 8 * (gk & 1), (gk >> 1) & 1);
+        if (kPaged) tc05::fence_async_smem();       // cp.async wrote through the generic proxy
+        tc05::fence_after_sync();
+        issue_qk(i, gk);
+        tc05::mma_commit_w(leader, bar_s + 8 * i);
+      };
+      if (!(started & 1)) first_qk(0, n, cB, g0);
+      stamp(p.dbg, tl, 2, g0, 6);
+      if (nB && !(started & 2)) first_qk(1, n, cB, g0);
+      if (!k0_released) tc05::mma_commit_w(leader, bar_ke + 8 * (g0 & 1));   // K_0 is free once these have run
+      if (nA == 1) tc05::mma_commit_w(leader, bar_qe);
+      if (nB == 1) tc05::mma_commit_w(leader, bar_qe1);
+      const int cB_next = cB + (nB ? 1 : 0);
+      started = 0;
+      k0_released = false;
+      Item nx;
+      bool peeked = false, have_next = false;
       for (int j = 0; j < nmax; ++j) {
         const int g = g0 + j, s = g & 1;
         const bool more_k = j + 1 < nmax;
         mbar_wait(bar_vf + 8 * s, (g >> 1) & 1);
         if (kPaged) tc05::fence_async_smem();
-        stamp(p.dbg, tl, 2, j, 4);
+        stamp(p.dbg, tl, 2, g, 4);
 #pragma unroll
         for (int i = 0; i < 2; ++i) {
           const int ni = i ? nB : nA;
@@ -421,7 +454,7 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant
             const uint32_t php = (cs[i] + j) & 1;
             mbar_wait(bar_ph + 8 * i, php);
             tc05::fence_after_sync();
-            stamp(p.dbg, tl, 2, j, 2 * i);
+            stamp(p.dbg, tl, 2, g, 2 * i);
             issue_pv(i, g, j == 0, 0);
             mbar_wait(bar_p + 8 * i, php);
             tc05::fence_after_sync();
@@ -433,19 +466,34 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant
               }
               issue_qk(i, g + 1);
               tc05::mma_commit_w(leader, bar_s + 8 * i);
+              if (j + 2 == ni) tc05::mma_commit_w(leader, i ? bar_qe1 : bar_qe);   // tile i's last Q.K^T: Q_i may go
             } else {
               tc05::mma_commit_w(leader, bar_o + 8 * i);
+              // Tile i of this item is done on the tensor core.  Its group still has the output to write, but S_i
+              // is free (the last P_i has been consumed, in order): the NEXT item's first Q_i.K_0^T goes in right
+              // here, so that group i finds its S ready when it comes out of the epilogue instead of waiting for
+              // the other tile's tail (B's diagonal tile and its softmax) to pass through the issuer first.
+              if (!peeked) { have_next = peek_item(n, nx); peeked = true; }
+              if (have_next && (i == 0 || nx.nB)) {
+                first_qk(i, n + 1, cB_next, g0 + nmax);
+                started |= 1 << i;
+                stamp(p.dbg, tl, 2, g, 5);
+              }
             }
-            stamp(p.dbg, tl, 2, j, 2 * i + 1);
+            stamp(p.dbg, tl, 2, g, 2 * i + 1);
           }
         }
         tc05::mma_commit_w(leader, bar_ve + 8 * s);   // V_j and K_{j+1} are consumed by everything issued so far
         if (more_k) tc05::mma_commit_w(leader, bar_ke + 8 * (s ^ 1));
-        if (j + 2 == nmax) tc05::mma_commit_w(leader, bar_qe);   // the item's last Q.K^T is among them
+      }
+      if (have_next && started == (nx.nB ? 3 : 1)) {  // both first products of the next item are in the queue
+        tc05::mma_commit_w(leader, bar_ke + 8 * ((g0 + nmax) & 1));
+        k0_released = true;
       }
       g0 += nmax;
       cs[0] += nA;
       cs[1] += nB;
+      cB = cB_next;
       if (!next_item(n, it, lane == 0)) break;
     }
     // the last commits must have landed in this CTA's shared memory before the CTA may exit
@@ -469,20 +517,21 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant
       const int head = it.head, qtok0 = it.qtok0, qlen = it.qlen, klen = it.klen, koff = it.koff;
       const int qi0 = it.q0 + 128 * grp;            // first row of this tile inside the prompt
       const bool dump = p.dbg && head == 0 && it.tile == 0 && grp == 0;
-      const bool tl = p.dbg && head == 0 && it.tile == 0 && r == 0;
+      const bool tl = p.dbg && blockIdx.x == 0 && blockIdx.y == 0 && r == 0;
       float m_run = -CUDART_INF_F, l_run = 0.f;
       // The exponentials of a tile keep the SM's special-function unit busy for as long as the tensor core
       // needs for that tile's two matrix products.  Left alone, the two groups drift into phase -- both in
       // their exponentials (sharing the unit), then both waiting for the tensor core -- and each unit idles
       // half of the time.  So the exponential section is a critical section that alternates A, B, A, B, ...:
       // while one group is in it the tensor core runs the other tile's P.V and next Q.K^T.
+      // A's first tile of an item takes no turn (it may share the unit with the tail of B's previous item; waiting
+      // for B to get there cost 2000 clk per item), from then on the two alternate.
       const bool pingpong = nB > 0;
-      if (pingpong && grp == 1) named_arrive(bar_other);          // A goes first
       for (int j = 0; j < ni; ++j) {
-        stamp(p.dbg, tl, grp, j, 0);
+        stamp(p.dbg, tl, grp, cs + j, 0);
         mbar_wait(bar_s + 8 * grp, (cs + j) & 1);
         tc05::fence_after_sync();
-        stamp(p.dbg, tl, grp, j, 1);
+        stamp(p.dbg, tl, grp, cs + j, 1);
         uint32_t s[4][32];
 #pragma unroll
         for (int c = 0; c < 4; ++c) tc05::tmem_ld32(tS + c * 32, s[c]);
@@ -536,13 +585,13 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant
         }
         const float neg_m = -m_run;
         float sum[4] = {0.f, 0.f, 0.f, 0.f};
-        stamp(p.dbg, tl, grp, j, 2);
-        if (pingpong && j < nA) named_sync(bar_mine);   // B's extra (diagonal) tile runs after A's last: no turn to wait for
+        stamp(p.dbg, tl, grp, cs + j, 2);
+        if (pingpong && j < nA && (grp == 1 || j > 0)) named_sync(bar_mine);   // B's extra (diagonal) tile runs after A's last: no turn to wait for
         // ptxas moves arithmetic (and MUFU) across BAR.SYNC freely; what it cannot move is a value loaded
         // after the barrier, so the section's multiplier is re-read from shared memory here
         float sc;
         asm volatile("ld.volatile.shared.f32 %0, [%1];" : "=f"(sc) : "r"(sc_slot) : "memory");
-        stamp(p.dbg, tl, grp, j, 3);
+        stamp(p.dbg, tl, grp, cs + j, 3);
 #pragma unroll
         for (int c2 = 0; c2 < 2; ++c2) {
           uint32_t pk[32];
@@ -561,20 +610,20 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant
             tc05::tmem_wait_st();
             tc05::fence_before_sync();
             mbar_arrive(bar_ph + 8 * grp);
-            stamp(p.dbg, tl, grp, j, 7);
+            stamp(p.dbg, tl, grp, cs + j, 7);
           }
         }
-        stamp(p.dbg, tl, grp, j, 4);
+        stamp(p.dbg, tl, grp, cs + j, 4);
         // hand over: B after its tile j lets A into tile j + 1 (if A has one); A after tile j lets B into tile j.
         // Every arrive is matched by exactly one later sync of the other group before the next arrive on the same
         // barrier can happen (two back-to-back arrives would complete the barrier with nobody waiting); the
-        // counts balance within an item (A syncs nA times: B's opening arrive + nA - 1; B syncs nA times).
+        // counts balance within an item (A syncs nA - 1 times, B arrives nA - 1 times; B syncs nA times).
         if (pingpong && (grp == 0 || j + 1 < nA)) named_arrive(bar_other);
         l_run += (sum[0] + sum[1]) + (sum[2] + sum[3]);
         tc05::tmem_wait_st();
         tc05::fence_before_sync();
         mbar_arrive(bar_p + 8 * grp);
-        stamp(p.dbg, tl, grp, j, 5);
+        stamp(p.dbg, tl, grp, cs + j, 5);
       }
       cs += ni;
       // ---- epilogue: O / l -> out ---------------------------------------------------------
@@ -586,11 +635,10 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant
       // (use u = 2 n + group waits for the u-th release); a group without a tile only passes the turn on.
       if (r == 0) mbar_wait(bar_stg, (grp & 1) ^ 1);   // u & 1 == group
       if (ni > 0) {
-        stamp(p.dbg, tl, grp, kTlIters - 1, 0);
         mbar_wait(bar_o + 8 * grp, co & 1);
         ++co;
         tc05::fence_after_sync();
-        stamp(p.dbg, tl, grp, kTlIters - 1, 1);
+        stamp(p.dbg, tl, grp, cs - 1, 6);             // O ready (the item's last P.V has run)
         const int D = p.head_size;
         const float inv = 1.f / l_run;
         named_sync_n(3 + grp, 128);                   // row 0's thread has seen the buffer released
@@ -642,6 +690,7 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant
         }
       }
       if (r == 0) mbar_arrive(bar_stg);
+      if (ni > 0) stamp(p.dbg, tl, 3, cs - 1, grp);     // output written (row 3 of the stamp table)
       if (!next_item(n, it, true)) break;
     }
   }
