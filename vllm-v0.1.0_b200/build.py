@@ -50,10 +50,28 @@ def _digest(paths) -> str:
     return h.hexdigest()
 
 
+def _deps(src: str):
+    """The source plus the project headers it includes, transitively (quoted includes only), so that an
+    edit to one kernel family's header does not recompile the others."""
+    seen, todo = [], [os.path.join(CSRC, src)]
+    while todo:
+        p = todo.pop()
+        if p in seen:
+            continue
+        seen.append(p)
+        with open(p) as f:
+            for line in f:
+                if line.startswith('#include "'):
+                    name = line.split('"')[1]
+                    cand = [os.path.join(CSRC, name), os.path.join(ROOT, "include", name)]
+                    todo += [c for c in cand if os.path.exists(c)]
+    return [seen[0]] + sorted(seen[1:])
+
+
 def _compile(nvcc: str, src: str, verbose: bool) -> str:
     obj = os.path.join(BUILD, src.replace(".cu", ".o"))
     stamp = obj + ".sha"
-    want = _digest([os.path.join(CSRC, src)] + HEADERS)
+    want = _digest(_deps(src))
     if os.path.exists(obj) and os.path.exists(stamp) and open(stamp).read() == want:
         return obj
     cmd = [nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-c", os.path.join(CSRC, src), "-o", obj]
@@ -133,7 +151,7 @@ def stale_objects():
     out = []
     for src in SOURCES:
         stamp = os.path.join(BUILD, src.replace(".cu", ".o")) + ".sha"
-        want = _digest([os.path.join(CSRC, src)] + HEADERS)
+        want = _digest(_deps(src))
         if not (os.path.exists(stamp) and open(stamp).read() == want):
             out.append(src)
     return out

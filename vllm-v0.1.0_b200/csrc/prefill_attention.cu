@@ -133,6 +133,42 @@ static int make_qkv_map(CUtensorMap* map, const void* base, int dtype, int head_
   return PA_OK;
 }
 
+// Tensor maps over the paged caches for the prompt kernel's page producer (prefill_tc.cuh).  The number of blocks
+// is not part of the operator's interface, so the outermost extent is a bound on (block, head) rows, not the
+// allocation: TMA only ever touches the boxes it is asked for.
+//   K [block][head][D/8][B][8]: (64 elements = 8 tokens x 8 = one 128-byte core matrix, B/8 token groups, D/8 chunks,
+//     block * heads + head), box 64 x 1 x D/8 x 1, no swizzle
+//   V [block][head][D][B]: (B tokens, D rows, block * heads + head), box B x D x 1, swizzle = the row size
+//     (B = 8: 16-byte rows, none; 16: 32 B; 32: 64 B)
+static int make_page_maps(CUtensorMap* mk, CUtensorMap* mv, const void* key_cache, const void* value_cache, int dtype,
+                          int head_size, int block_size) {
+  EncodeTiledFn fn = encode_tiled_fn();
+  if (!fn) return set_error(PA_ERR_CUDA, "cuTensorMapEncodeTiled is not available from this driver");
+  const CUtensorMapDataType dt = dtype == PA_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16;
+  const cuuint64_t rows = cuuint64_t{1} << 30;
+  const cuuint64_t page_bytes = static_cast<cuuint64_t>(head_size) * block_size * 2;
+  const cuuint32_t estr[4] = {1, 1, 1, 1};
+  {
+    const cuuint64_t dims[4] = {64, static_cast<cuuint64_t>(block_size / 8), static_cast<cuuint64_t>(head_size / 8), rows};
+    const cuuint64_t strides[3] = {128, static_cast<cuuint64_t>(block_size) * 16, page_bytes};
+    const cuuint32_t box[4] = {64, 1, static_cast<cuuint32_t>(head_size / 8), 1};
+    const CUresult r = fn(mk, dt, 4, const_cast<void*>(key_cache), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                          CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return set_error(PA_ERR_CUDA, "cuTensorMapEncodeTiled (key pages) failed with CUresult %d", static_cast<int>(r));
+  }
+  {
+    const cuuint64_t dims[3] = {static_cast<cuuint64_t>(block_size), static_cast<cuuint64_t>(head_size), rows};
+    const cuuint64_t strides[2] = {static_cast<cuuint64_t>(block_size) * 2, page_bytes};
+    const cuuint32_t box[3] = {static_cast<cuuint32_t>(block_size), static_cast<cuuint32_t>(head_size), 1};
+    const CUtensorMapSwizzle sw = block_size == 8 ? CU_TENSOR_MAP_SWIZZLE_NONE
+                                  : block_size == 16 ? CU_TENSOR_MAP_SWIZZLE_32B : CU_TENSOR_MAP_SWIZZLE_64B;
+    const CUresult r = fn(mv, dt, 3, const_cast<void*>(value_cache), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                          sw, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return set_error(PA_ERR_CUDA, "cuTensorMapEncodeTiled (value pages) failed with CUresult %d", static_cast<int>(r));
+  }
+  return PA_OK;
+}
+
 template <typename T, int DP, bool kPaged>
 static int launch_tc(const CUtensorMap& mq, const CUtensorMap& mk, const CUtensorMap& mv, const CUtensorMap& mo,
                      const PrefillTiles& tiles,
@@ -209,7 +245,8 @@ static int prefill(void* out, const void* query, const void* key, const void* va
   const int dp = head_size <= 64 ? 64 : 128;
   if (dtype != PA_F32) {
     int rc = make_qkv_map(&mq, query, dtype, head_size, num_heads, tok, q_stride);
-    if (paged) { mk = mq; mv = mq; }               // unused by the paged kernel
+    if (rc == PA_OK && paged)
+      rc = make_page_maps(&mk, &mv, paged->key_cache, paged->value_cache, dtype, head_size, paged->block_size);
     if (rc == PA_OK && !paged) rc = make_qkv_map(&mk, key, dtype, head_size, num_heads, ktok, k_stride);
     if (rc == PA_OK && !paged) rc = make_qkv_map(&mv, value, dtype, head_size, num_heads, ktok, v_stride);
     if (rc == PA_OK) rc = make_qkv_map(&mo, out, dtype, head_size, num_heads, tok, out_stride);

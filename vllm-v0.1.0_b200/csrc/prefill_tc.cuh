@@ -63,19 +63,6 @@ struct PrefillParams {
   int32_t tile_major;
 };
 
-constexpr int kPfPageThreads = 96;   // warps 8, 10 and 11 copy pages when kPaged
-
-// 16 bytes global -> shared, the last 16 - src_bytes of them zero-filled (Ampere-style async copy: any
-// destination address per thread, which is what turns a cache page into a swizzled operand tile)
-__device__ __forceinline__ void cp_async16(uint32_t dst, const void* src, int src_bytes) {
-  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" :: "r"(dst), "l"(src), "r"(src_bytes) : "memory");
-}
-// the mbarrier receives one arrival (of its expected count) when all of this thread's earlier cp.async have completed
-__device__ __forceinline__ void cp_async_arrive(uint32_t bar) {
-  asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" :: "r"(bar) : "memory");
-}
-
-
 // tests / tools: SM-clock stamps of the hand-offs of CTA (head 0, tile 0) into the debug buffer, after the raw
 // tiles: slot ((who * kTlIters + j) * 8 + event), who = 0 / 1 softmax group A / B, 2 issuer (tools/prefill_timeline.py)
 constexpr int kTlBase = 40000, kTlIters = 40;
@@ -140,7 +127,6 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant
   // V is the B operand of P.V: packed rows give an MN-major tile ([token][d]); cache pages give a K-major one
   // ([d][token], the page's own order)
   const uint32_t idesc_pv = tc05::instr_desc_f16(kBf16, 128, p.head_size, false, !kPaged);
-  constexpr uint32_t kVAtomBytes = DP * 128;     // kPaged: 64 tokens (128 bytes) of every d row
   const int qk_steps = p.head_size / 16;
   constexpr uint32_t kTmS = 0, kTmO = 256, kTmCols = 512;   // S_i at 128 i, O_i at 256 + 128 i
 
@@ -159,6 +145,7 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant
   const uint32_t bar_stg = sBar + 152;             // the staging buffer's previous user is done with it
   const uint32_t bar_cf = sBar + 160, bar_ce = sBar + 176;   // [2] each: next work item landed / read by everybody
   const uint32_t sClc = sBar + 192;                // [2] x 16 bytes: the scheduler's answers
+  const uint32_t bar_vl = sBar + 240;              // kPaged: a V tile whose tail is zeroed lands here first
   const uint32_t tm_slot = sBar + 120;
   const uint32_t sc_slot = sBar + 124;             // scale_log2, re-read after the ping-pong barrier (see below)
 
@@ -187,7 +174,7 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant
   // Item n + 1 of this CTA is the answer to the n-th request (slot n & 1), issued by the scheduler thread when
   // it starts item n.  Every thread that works on items calls next_item() once per item, in order: it waits for
   // the answer, reads it, releases the slot, and learns whether to go on.
-  constexpr uint32_t kClcReaders = 256 + 1 + (kPaged ? kPfPageThreads : 1);   // softmax threads, issuer lane, producers
+  constexpr uint32_t kClcReaders = 256 + 1 + 1;    // softmax threads, issuer lane, producer lane
   auto request_next = [&](int n) {                // scheduler thread only
     const uint32_t slot = n & 1;
     mbar_wait(bar_ce + 8 * slot, ((n >> 1) & 1) ^ 1);   // first use of a slot passes immediately
@@ -221,9 +208,10 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant
     mbar_init(bar_q, 1); mbar_init(bar_q1, 1);
     mbar_init(bar_qe, 1); mbar_init(bar_qe1, 1);
     mbar_init(bar_stg, 1);
+    mbar_init(bar_vl, 1);
     for (int s = 0; s < 2; ++s) {
-      mbar_init(bar_kf + 8 * s, kPaged ? kPfPageThreads : 1); mbar_init(bar_ke + 8 * s, 1);
-      mbar_init(bar_vf + 8 * s, kPaged ? kPfPageThreads : 1); mbar_init(bar_ve + 8 * s, 1);
+      mbar_init(bar_kf + 8 * s, 1); mbar_init(bar_ke + 8 * s, 1);
+      mbar_init(bar_vf + 8 * s, 1); mbar_init(bar_ve + 8 * s, 1);
       mbar_init(bar_s + 8 * s, 1); mbar_init(bar_p + 8 * s, 128); mbar_init(bar_o + 8 * s, 1);
       mbar_init(bar_ph + 8 * s, 128);
       mbar_init(bar_cf + 8 * s, 1); mbar_init(bar_ce + 8 * s, kClcReaders);
@@ -238,82 +226,38 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant
   uint32_t tmem;
   asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem) : "r"(tm_slot) : "memory");
 
-  if (kPaged && (warp == 8 || warp >= 10)) {
+  if (kPaged && warp == 8) {
     // ===================== page producer (kPaged) =====================
-    // Three warps copy the K and V pages of the sequence into the operand tiles.  As 16-byte chunks a K page
-    // ([d / 8][token][8]) and a V page ([d][token]) are permutations of the 128-byte-swizzled K-major tiles
-    // tcgen05.mma reads (K: row = token, chunk = d / 8; V: row = d, chunk = token / 8), so every thread moves
-    // chunks with cp.async to the address the swizzle dictates: global reads stay page-contiguous, no gather
-    // pass, no scratch.  Tokens past the context are zero-filled by the copy itself (never-written slots of the
-    // last page may hold anything; 0 x NaN must not reach O).  Nobody waits for a copy: each thread hangs an
-    // arrival on the tile's full-barrier behind its copies (cp.async.mbarrier.arrive.noinc) and moves on to the
-    // next free stage, so up to the whole ring is in flight; the issuer crosses to the async proxy with a proxy
-    // fence after its barrier wait.
+    // One warp, no per-thread copies: a cache page already IS an operand tile of tcgen05.mma, so whole pages go
+    // from HBM to shared memory by TMA.
+    //   K page [d / 8][token][8]: for one 8-token group the D / 8 chunks are 128 contiguous bytes each = the
+    //     8-row x 16-byte core matrices of the no-swizzle K-major layout.  Tensor map (64 elements = one core
+    //     matrix, token group, chunk, block * heads + head), box 64 x 1 x D/8 x 1: group G of the tile lands at
+    //     G * D * 16 bytes as [chunk][8 tokens][16 B] -> LBO (next K chunk) 128 B, SBO (next token group) D * 16.
+    //   V page [d][token]: rows of B tokens = 16 / 32 / 64 bytes, K-major with N = d.  Tensor map (token, d,
+    //     block * heads + head), box B x D x 1 with no / 32-byte / 64-byte swizzle: a page of 16 tokens is one MMA
+    //     k-step (SBO 256 B), of 32 tokens two (start address + 32 B), two pages of 8 tokens make one (LBO = page).
+    // Lane G issues K group G, lane l V page l; block numbers are fetched one tile ahead (one coalesced load) and
+    // passed by shuffle.  Pages beyond the context are not loaded (their k-steps of P.V are not issued, their
+    // logits are masked by selection); in the context's last k-step the tokens past the end are zeroed in shared
+    // memory behind the TMA (never-written slots may hold NaN; 0 x NaN must not reach O).
     asm volatile("setmaxnreg.dec.sync.aligned.u32 56;");
-    const int pt = (warp == 8 ? 0 : warp - 9) * 32 + lane;          // 0 .. 95
     const int shB = p.block_shift, B = 1 << shB;
-    const int D = p.head_size;
-    const int64_t page_bytes = static_cast<int64_t>(D) * B * 2;
-    const int64_t block_stride = page_bytes * p.num_heads;
-    const char* kc = static_cast<const char*>(p.key_cache);
-    const char* vc = static_cast<const char*>(p.value_cache);
+    const int D = p.head_size, H = p.num_heads;
     const int npg = kPfCols >> shB;                 // pages per 128-token tile
-    const int kchunks = (D >> 3) << shB;            // 16-byte chunks of a K page, of a V page likewise
-    const int iters = (kchunks + kPfPageThreads - 1) / kPfPageThreads;
-    int64_t head_off = 0;
+    const uint32_t kgrp_bytes = D * 16;             // one 8-token group of K: D / 8 core matrices
+    const uint32_t vpage_bytes = D * B * 2;
     const int32_t* table = nullptr;
     int klen = 0;
-    // block numbers of a tile's pages: lane l fetches page l's (one coalesced load per warp, issued a tile ahead
-    // so its latency hides behind the copies of the current tile), the page loops read them by shuffle
-    auto tile_blocks = [&](int t) {
+    auto tile_blocks = [&](int t) {                 // lane l: block number of page l of tile t
       const int ptok = t * kPfCols + (lane << shB);
       return (lane < npg && ptok < klen) ? __ldg(table + (ptok >> shB)) : 0;
     };
-    // The producer warps share their schedulers with the softmax warps, so instructions per copy are what
-    // counts: everything that does not depend on the page (the chunk's place in the page, its swizzled place
-    // in the tile) is computed once per thread-chunk, the page loop inside adds the page's base and copies.
-    auto load_k = [&](int t, uint32_t dst, int blocks) {
-      const int nvalid = klen - t * kPfCols;        // tokens of this tile inside the context
-      for (int i = 0; i < iters; ++i) {
-        const int idx = pt + i * kPfPageThreads;
-        const bool mine = idx < kchunks;
-        const int c = idx >> shB, tl = idx & (B - 1);
-        // row r = page * B + tl: r & 7 == tl & 7 (B is a multiple of 8), so the swizzle term is page-invariant
-        uint32_t d = dst + (c >> 3) * kAtomBytes + tl * 128 + (((c & 7) ^ (tl & 7)) << 4);
-        const char* src = kc + head_off + idx * 16;
-        int left = nvalid - tl;                     // > 0: this token of page 0 is inside the context
-#pragma unroll 4
-        for (int pg = 0; pg < npg; ++pg) {
-          const int64_t page = static_cast<int64_t>(__shfl_sync(0xffffffffu, blocks, pg)) * block_stride;
-          if (mine) cp_async16(d, src + page, left > 0 ? 16 : 0);
-          d += B * 128;
-          left -= B;
-        }
-      }
-    };
-    auto load_v = [&](int t, uint32_t dst, int blocks) {
-      const int shC = shB - 3;                      // log2(8-token chunks per d row of a page)
-      const int nvalid = klen - t * kPfCols;
-      for (int i = 0; i < iters; ++i) {
-        const int idx = pt + i * kPfPageThreads;
-        const bool mine = idx < kchunks;
-        const int d = idx >> shC, tcl = idx & ((1 << shC) - 1);
-        const uint32_t drow = dst + d * 128;
-        const char* src = vc + head_off + idx * 16;
-        int tc = tcl;                               // 8-token chunk of the tile: page * (B / 8) + tcl
-#pragma unroll 4
-        for (int pg = 0; pg < npg; ++pg) {
-          const int64_t page = static_cast<int64_t>(__shfl_sync(0xffffffffu, blocks, pg)) * block_stride;
-          const int nv = min(max(nvalid - tc * 8, 0), 8);
-          if (mine) cp_async16(drow + (tc >> 3) * kVAtomBytes + (((tc & 7) ^ (d & 7)) << 4), src + page, nv * 2);
-          tc += 1 << shC;
-        }
-      }
-    };
     int g = 0;                                      // K/V tiles loaded so far: the rings run on across items
     int cB = 0;                                     // items with a tile B so far (phases of bar_q1 / bar_qe1)
+    int ctail = 0;                                  // tiles with a zeroed tail so far (phase of bar_vl)
     for (int n = 0;; ++n) {
-      if (pt == 0) {
+      if (lane == 0) {
         request_next(n);
         if (n > 0) mbar_wait(bar_qe, (n - 1) & 1);  // the previous item's last Q_A.K^T has read Q_A
         mbar_expect_tx(bar_q, kTileBytes);
@@ -321,7 +265,7 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant
         for (int a = 0; a < kAtoms; ++a)
           tc05::tma_load_3d(sQ + a * kAtomBytes, &tmq, a * 64, it.head, it.qtok0 + it.q0, bar_q);
       }
-      head_off = page_bytes * it.head;
+      __syncwarp();
       table = p.block_tables + static_cast<int64_t>(it.ktok0) * p.max_blocks;   // ktok0 = sequence index
       klen = it.klen;
       int next_blocks = tile_blocks(0);
@@ -330,24 +274,64 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant
         const uint32_t ph = ((g >> 1) & 1) ^ 1;     // first use of a stage passes immediately
         const int blocks = next_blocks;
         if (j + 1 < it.nmax) next_blocks = tile_blocks(j + 1);
+        const int nvalid = min(klen - j * kPfCols, kPfCols);   // tokens of this tile inside the context (>= 1)
+        const int ngrp = (nvalid + 7) >> 3, npages = (nvalid + B - 1) >> shB;
+        const int row = blocks * H + it.head;       // lane l: (block, head) row of page l in both caches
         mbar_wait(bar_ke + 8 * s, ph);
-        load_k(j, sK + s * kTileBytes, blocks);
-        cp_async_arrive(bar_kf + 8 * s);            // arrives by itself once this thread's copies have landed
-        if (j == 0 && it.nB && pt == 0) {           // Q_B behind K_0: it is free one iteration later than Q_A
+        if (lane == 0) mbar_expect_tx(bar_kf + 8 * s, ngrp * kgrp_bytes);
+        __syncwarp();
+        {
+          const int krow = __shfl_sync(0xffffffffu, row, (lane << 3) >> shB);   // lane G: the page of group G
+          if (lane < ngrp)
+            tc05::tma_load_4d(sK + s * kTileBytes + lane * kgrp_bytes, &tmk, 0, lane & ((B >> 3) - 1), 0, krow,
+                              bar_kf + 8 * s);
+        }
+        if (j == 0 && it.nB && lane == 0) {         // Q_B behind K_0: it is free one iteration later than Q_A
           if (cB > 0) mbar_wait(bar_qe1, (cB - 1) & 1);
           mbar_expect_tx(bar_q1, kTileBytes);
 #pragma unroll
           for (int a = 0; a < kAtoms; ++a)
             tc05::tma_load_3d(sQ + kTileBytes + a * kAtomBytes, &tmq, a * 64, it.head, it.qtok0 + it.q0 + 128, bar_q1);
-          ++cB;
         }
+        if (j == 0 && it.nB) ++cB;
+        __syncwarp();
         mbar_wait(bar_ve + 8 * s, ph);
-        load_v(j, sV + s * kTileBytes, blocks);
-        cp_async_arrive(bar_vf + 8 * s);
+        const bool tail = (nvalid & 15) != 0;       // the last k-step holds tokens past the context
+        const uint32_t vbar = tail ? bar_vl : bar_vf + 8 * s;
+        if (lane == 0) mbar_expect_tx(vbar, npages * vpage_bytes);
+        __syncwarp();
+        const uint32_t vdst = sV + s * kTileBytes;
+        if (lane < npages) tc05::tma_load_3d(vdst + lane * vpage_bytes, &tmv, 0, 0, row, vbar);
+        if (tail) {
+          mbar_wait(bar_vl, ctail & 1);
+          ++ctail;
+          const int ks = (nvalid - 1) >> 4;         // the k-step to repair; vt of its 16 tokens are valid
+          const int vt = nvalid - ks * 16;
+          for (int idx = lane; idx < 2 * D; idx += 32) {
+            const int d = idx >> 1, h = idx & 1;    // 16-byte chunk h (8 tokens) of row d of this k-step
+            const int nv = min(max(vt - 8 * h, 0), 8);
+            if (nv == 8) continue;
+            uint32_t a;
+            if (shB == 4) a = ks * vpage_bytes + d * 32 + ((h ^ ((d >> 2) & 1)) << 4);
+            else if (shB == 5) a = (ks >> 1) * vpage_bytes + d * 64 + ((((ks & 1) * 2 + h) ^ ((d >> 1) & 3)) << 4);
+            else a = (2 * ks + h) * vpage_bytes + d * 16;
+            a += vdst;
+            uint32_t w[4] = {0u, 0u, 0u, 0u};
+            if (nv > 0) {
+              asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(w[0]), "=r"(w[1]), "=r"(w[2]), "=r"(w[3]) : "r"(a) : "memory");
+#pragma unroll
+              for (int e = 0; e < 4; ++e)
+                w[e] = 2 * e >= nv ? 0u : (2 * e + 1 >= nv ? w[e] & 0xffffu : w[e]);
+            }
+            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" :: "r"(a), "r"(w[0]), "r"(w[1]), "r"(w[2]), "r"(w[3]) : "memory");
+          }
+          tc05::fence_async_smem();                 // generic-proxy stores -> visible to the MMA's reads
+          __syncwarp();
+          if (lane == 0) mbar_arrive(bar_vf + 8 * s);
+        }
       }
-      if (!next_item(n, it, true)) break;
+      if (!next_item(n, it, lane == 0)) break;
     }
-    asm volatile("cp.async.wait_all;" ::: "memory");   // nothing of this thread's may be in flight when the CTA exits
   } else if (warp == 8) {
     // ===================== TMA producer =====================
     asm volatile("setmaxnreg.dec.sync.aligned.u32 56;");
@@ -392,22 +376,31 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant
     const bool leader = tc05::elect_one();
     const uint32_t tm = __shfl_sync(0xffffffffu, tmem, 0);
     auto desc = [](uint64_t base, uint32_t byte_off) { return base + (byte_off >> 4); };
-    const uint64_t dq = tc05::smem_desc_sw128(sQ, 16, 1024), dk = tc05::smem_desc_sw128(sK, 16, 1024);
-    const uint64_t dv = kPaged ? tc05::smem_desc_sw128(sV, 16, 1024) : tc05::smem_desc_sw128(sV, kAtomBytes, 1024);
+    // kPaged: the operand tiles are the cache pages as the producer's TMA boxes left them (see there)
+    const int shB = p.block_shift;
+    const uint32_t vstep = p.head_size * 32;        // bytes of V per 16-token k-step (all d rows)
+    const uint64_t dq = tc05::smem_desc_sw128(sQ, 16, 1024);
+    const uint64_t dk = kPaged ? tc05::smem_desc(sK, 128, p.head_size * 16, 0) : tc05::smem_desc_sw128(sK, 16, 1024);
+    const uint64_t dv = !kPaged ? tc05::smem_desc_sw128(sV, kAtomBytes, 1024)
+                        : shB == 4 ? tc05::smem_desc(sV, 16, 256, 6)
+                        : shB == 5 ? tc05::smem_desc(sV, 16, 512, 4)
+                                   : tc05::smem_desc(sV, p.head_size * 16, 128, 0);
     auto issue_qk = [&](int i, int g) {             // S_i = Q_i . K^T, K in ring slot g
       const uint64_t qb = desc(dq, i * kTileBytes), kb = desc(dk, (g & 1) * kTileBytes);
 #pragma unroll
       for (int kk = 0; kk < DP / 16; ++kk) {
         if (kk >= qk_steps) break;
         const uint32_t off = (kk >> 2) * kAtomBytes + (kk & 3) * 32;
-        tc05::mma_ss_w(leader, tm + kTmS + 128 * i, desc(qb, off), desc(kb, off), kIdescQK, kk > 0);
+        tc05::mma_ss_w(leader, tm + kTmS + 128 * i, desc(qb, off), desc(kb, kPaged ? kk * 256 : off), kIdescQK, kk > 0);
       }
     };
-    auto issue_pv = [&](int i, int g, bool first, int half) {   // O_i (+)= P_i . V, keys 64 half .. 64 half + 63 of the tile
+    // O_i (+)= P_i . V, keys 64 half .. 64 half + 63 of the tile; kmax: k-steps that hold keys of the context
+    auto issue_pv = [&](int i, int g, bool first, int half, int kmax) {
       const uint64_t vb = desc(dv, (g & 1) * kTileBytes);
 #pragma unroll
       for (int kk = half * (kPfCols / 32); kk < (half + 1) * (kPfCols / 32); ++kk) {
-        const uint32_t off = kPaged ? (kk >> 2) * kVAtomBytes + (kk & 3) * 32 : kk * 2048;
+        if (kPaged && kk >= kmax) break;
+        const uint32_t off = !kPaged ? kk * 2048 : shB == 5 ? (kk >> 1) * 2 * vstep + (kk & 1) * 32 : kk * vstep;
         tc05::mma_ts_w(leader, tm + kTmO + 128 * i, tm + kTmS + 128 * i + kk * 8, desc(vb, off), idesc_pv, !first || kk > 0);
       }
     };
@@ -423,7 +416,6 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant
       auto first_qk = [&](int i, int item, int cb, int gk) {
         mbar_wait(i ? bar_q1 : bar_q, (i ? cb : item) & 1);
         mbar_wait(bar_kf + 8 * (gk & 1), (gk >> 1) & 1);
-        if (kPaged) tc05::fence_async_smem();       // cp.async wrote through the generic proxy
         tc05::fence_after_sync();
         issue_qk(i, gk);
         tc05::mma_commit_w(leader, bar_s + 8 * i);
@@ -443,7 +435,7 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant
         const int g = g0 + j, s = g & 1;
         const bool more_k = j + 1 < nmax;
         mbar_wait(bar_vf + 8 * s, (g >> 1) & 1);
-        if (kPaged) tc05::fence_async_smem();
+        const int kmax = kPaged ? (min(it.klen - j * kPfCols, kPfCols) + 15) >> 4 : kPfCols / 16;
         stamp(p.dbg, tl, 2, g, 4);
 #pragma unroll
         for (int i = 0; i < 2; ++i) {
@@ -455,14 +447,13 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant
             mbar_wait(bar_ph + 8 * i, php);
             tc05::fence_after_sync();
             stamp(p.dbg, tl, 2, g, 2 * i);
-            issue_pv(i, g, j == 0, 0);
+            issue_pv(i, g, j == 0, 0, kmax);
             mbar_wait(bar_p + 8 * i, php);
             tc05::fence_after_sync();
-            issue_pv(i, g, false, 1);
+            issue_pv(i, g, false, 1, kmax);
             if (j + 1 < ni) {
               if (i == 0 || j + 1 >= nA) {          // K_{j+1} is needed from here on, not before the P.V above
                 mbar_wait(bar_kf + 8 * (s ^ 1), ((g + 1) >> 1) & 1);
-                if (kPaged) tc05::fence_async_smem();
               }
               issue_qk(i, g + 1);
               tc05::mma_commit_w(leader, bar_s + 8 * i);

@@ -31,6 +31,20 @@ __device__ __forceinline__ uint64_t smem_desc_sw128(uint32_t smem_byte_addr, uin
          (static_cast<uint64_t>((sbo_bytes >> 4) & 0x3fffu) << 32);
 }
 
+// Any canonical layout: swizzle code 0 (none: 8-row x 16-byte core matrices of 128 contiguous bytes), 2 (128 B),
+// 4 (64 B), 6 (32 B).  K-major operands (cute's canonical forms, in 16-byte units):
+//   none  ((8,n),2):((1,SBO),LBO)   rows 16 B apart inside a core matrix, 8-row groups SBO apart, the two
+//                                   16-byte K chunks of one MMA k-step LBO apart
+//   32 B  ((8,n),2):((2,SBO),1)     rows 32 B apart (one k-step per row), 8-row groups SBO (= 256 B dense) apart
+//   64 B  ((8,n),2):((4,SBO),1)     rows 64 B apart (two k-steps per row, +32 B start address for the second)
+__device__ __forceinline__ uint64_t smem_desc(uint32_t smem_byte_addr, uint32_t lbo_bytes, uint32_t sbo_bytes,
+                                              uint32_t swizzle_code) {
+  return (uint64_t{1} << 46) | (static_cast<uint64_t>(swizzle_code) << 61) |
+         static_cast<uint64_t>((smem_byte_addr & 0x3ffffu) >> 4) |
+         (static_cast<uint64_t>((lbo_bytes >> 4) & 0x3fffu) << 16) |
+         (static_cast<uint64_t>((sbo_bytes >> 4) & 0x3fffu) << 32);
+}
+
 // ---------------------------------------------------------------------------
 // instruction descriptor of tcgen05.mma.kind::f16 (32 bit, passed in the upper half of nothing:
 // the PTX operand is the 32-bit value itself)
@@ -148,6 +162,11 @@ __device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap* map
   asm volatile(
       "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
       :: "r"(dst), "l"(reinterpret_cast<uint64_t>(map)), "r"(bar), "r"(c0), "r"(c1), "r"(c2) : "memory");
+}
+__device__ __forceinline__ void tma_load_4d(uint32_t dst, const CUtensorMap* map, int c0, int c1, int c2, int c3, uint32_t bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];"
+      :: "r"(dst), "l"(reinterpret_cast<uint64_t>(map)), "r"(bar), "r"(c0), "r"(c1), "r"(c2), "r"(c3) : "memory");
 }
 // Cluster launch control: a running CTA asks the hardware scheduler for the next CTA of the grid that has not
 // started yet.  16-byte answer in shared memory, completion (16 bytes) counted on `bar`.  Canceled = that CTA will
