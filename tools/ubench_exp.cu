@@ -40,6 +40,27 @@ __device__ __forceinline__ uint32_t pack_bf16_trunc(float lo, float hi) {
   return r;
 }
 
+// packed 16-bit exponentials: one MUFU lane-op gives two results, already in the P operand's format
+__device__ __forceinline__ uint32_t ex2_bf16x2(uint32_t x) { uint32_t y; asm volatile("ex2.approx.ftz.bf16x2 %0, %1;" : "=r"(y) : "r"(x)); return y; }
+__device__ __forceinline__ uint32_t ex2_f16x2(uint32_t x) { uint32_t y; asm volatile("ex2.approx.f16x2 %0, %1;" : "=r"(y) : "r"(x)); return y; }
+__device__ __forceinline__ uint32_t pack_f16(float lo, float hi) {
+  uint32_t r; asm("cvt.rn.f16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo)); return r;
+}
+__device__ __forceinline__ float sum_bf16_lo(uint32_t a, float c) {   // c + lo(a) * 1.0, exact (FHFMA)
+  float d; asm("{.reg .b16 al, ah, o;\n\tmov.b32 {al, ah}, %1; mov.b16 o, 0x3f80;\n\tfma.rn.f32.bf16 %0, al, o, %2;}" : "=f"(d) : "r"(a), "f"(c)); return d;
+}
+__device__ __forceinline__ float sum_bf16_hi(uint32_t a, float c) {
+  float d; asm("{.reg .b16 al, ah, o;\n\tmov.b32 {al, ah}, %1; mov.b16 o, 0x3f80;\n\tfma.rn.f32.bf16 %0, ah, o, %2;}" : "=f"(d) : "r"(a), "f"(c)); return d;
+}
+__device__ __forceinline__ float sum_f16_lo(uint32_t a, float c) {
+  float d; asm("{.reg .b16 al, ah, o;\n\tmov.b32 {al, ah}, %1; mov.b16 o, 0x3c00;\n\tfma.rn.f32.f16 %0, al, o, %2;}" : "=f"(d) : "r"(a), "f"(c)); return d;
+}
+__device__ __forceinline__ float sum_f16_hi(uint32_t a, float c) {
+  float d; asm("{.reg .b16 al, ah, o;\n\tmov.b32 {al, ah}, %1; mov.b16 o, 0x3c00;\n\tfma.rn.f32.f16 %0, ah, o, %2;}" : "=f"(d) : "r"(a), "f"(c)); return d;
+}
+// mode 8 / 9: ffma2 -> pack the two arguments -> ONE packed ex2 (bf16x2 / f16x2) = P as stored -> two mixed-precision adds
+// mode 10: as 8, sums by shift / mask + fadd2
+// mode 11: 64 x ex2.bf16x2 alone
 // mode 5 / 6 / 7: the kernel's section with the pack on the integer pipe (2 adds + prmt / 64-bit add + prmt / prmt only)
 // mode 0: 128 ex2 only (sum by plain adds at the end)
 // mode 1: the kernel's section: ffma2 -> 2 x ex2 (volatile) -> fadd2 + pack, per pair
@@ -63,6 +84,20 @@ __global__ void __launch_bounds__(128, 1) k(const float* __restrict__ in, float*
   if (MODE == 0) {
 #pragma unroll
     for (int i = 0; i < 128; ++i) s[i] = ex2v(s[i]);
+  } else if (MODE == 11) {
+#pragma unroll
+    for (int i = 0; i < 64; ++i) pk[i] = ex2_bf16x2(__float_as_uint(s[i]));
+  } else if (MODE >= 8) {
+#pragma unroll
+    for (int i = 0; i < 128; i += 2) {
+      float a0, a1;
+      ffma2(a0, a1, s[i], s[i + 1], sc, nm);
+      const uint32_t pp = MODE == 9 ? ex2_f16x2(pack_f16(a0, a1)) : ex2_bf16x2(pack_bf16(a0, a1));
+      if (MODE == 8) { sum[(i >> 1) & 1] = sum_bf16_lo(pp, sum[(i >> 1) & 1]); sum[2 + ((i >> 1) & 1)] = sum_bf16_hi(pp, sum[2 + ((i >> 1) & 1)]); }
+      if (MODE == 9) { sum[(i >> 1) & 1] = sum_f16_lo(pp, sum[(i >> 1) & 1]); sum[2 + ((i >> 1) & 1)] = sum_f16_hi(pp, sum[2 + ((i >> 1) & 1)]); }
+      if (MODE == 10) fadd2(sum[(i >> 1) & 1 ? 2 : 0], sum[(i >> 1) & 1 ? 3 : 1], __uint_as_float(pp << 16), __uint_as_float(pp & 0xffff0000u));
+      pk[i >> 1] = pp;
+    }
   } else {
 #pragma unroll
     for (int i = 0; i < 128; i += 2) {
@@ -81,6 +116,7 @@ __global__ void __launch_bounds__(128, 1) k(const float* __restrict__ in, float*
 #pragma unroll
     for (int i = 0; i < 128; ++i) acc += s[i];
   } else {
+    if (MODE == 11) acc += s[127];
     uint32_t x = 0;
 #pragma unroll
     for (int i = 0; i < 64; ++i) x ^= pk[i];
@@ -113,5 +149,9 @@ int main() {
   run<5>("5: kernel section, pack = 2 x IADD + PRMT", in, out, clk);
   run<6>("6: kernel section, pack = 64-bit add + PRMT", in, out, clk);
   run<7>("7: kernel section, pack = PRMT (truncation)", in, out, clk);
+  run<11>("11: 64 x ex2.bf16x2 alone (= 128 exponentials)", in, out, clk);
+  run<8>("8: ffma2, pack args, ex2.bf16x2, 2 x fma.f32.bf16 sums", in, out, clk);
+  run<9>("9: ffma2, pack args, ex2.f16x2, 2 x fma.f32.f16 sums", in, out, clk);
+  run<10>("10: as 8, sums by shl / and + fadd2", in, out, clk);
   return 0;
 }
