@@ -233,6 +233,38 @@ def test_untouched_rows_unwritten_slots_and_errors():
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("dt", ["f16", "bf16"])
+@pytest.mark.parametrize("d,b", [(128, 8), (128, 16), (128, 32), (64, 16), (64, 32), (80, 8), (80, 16), (96, 32)])
+def test_every_tail_of_every_page_layout(dt, d, b):
+    """The page producer hands cache pages to the tensor core as they lie (K: no-swizzle core matrices, V: rows of
+    8 / 16 / 32 tokens without / with 32-byte / 64-byte swizzle) and repairs the context's last k-step in shared
+    memory.  Contexts ending at every position of a 16-token k-step, in the first and in later tiles, with NaN in
+    every slot past each context and in every block no table names: nothing of it may reach the output."""
+    dtype = cases.DTYPES[dt]
+    ctxs = list(range(1, 34)) + [120 + r for r in range(0, 18)] + [256 + r for r in (1, 7, 8, 9, 15, 16, 17, 24, 25, 31)]
+    pairs = [(min(c, 1 + i % 4), c) for i, c in enumerate(ctxs)]
+    c = _random_problem(dtype, d, b, pairs, h=2, seed=d * 7 + b)
+    kc, vc = c["key_cache"].clone(), c["value_cache"].clone()
+    named = torch.zeros(kc.shape[0], dtype=torch.bool)
+    for i, (_, n) in enumerate(pairs):
+        nb = (n + b - 1) // b
+        named[c["block_tables"][i, :nb].long()] = True
+        if n % b:
+            last = int(c["block_tables"][i, nb - 1])
+            kc[last, :, :, n % b:, :] = float("nan")
+            vc[last, :, :, n % b:] = float("nan")
+    kc[~named] = float("nan")
+    vc[~named] = float("nan")
+    # padding entries of the tables name block 0: make sure it is somebody's real block or poisoned
+    c["key_cache"], c["value_cache"] = kc, vc
+    got = _run(c)
+    assert torch.isfinite(got.float()).all(), "NaN from an unwritten slot reached the output"
+    truth = paged_oracle.cached_prefill_attention_fp32(c["cu_query_lens"], c["query"], kc, vc, c["block_tables"],
+                                                       c["context_lens"], c["scale"])
+    _close(got, truth, dtype, f"{dt} d{d} b{b}")
+
+
+@pytest.mark.gpu
 def test_grid_order_does_not_change_results():
     """Same property for the paged kernel: 6 chunks over 4000-token contexts, 10 heads (123 MB of K/V: tiles fastest)
     against the same sequences in two calls of 3 (heads fastest), bit for bit."""
