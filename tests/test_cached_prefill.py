@@ -278,16 +278,50 @@ def test_grid_order_does_not_change_results():
     kc, vc, bt = c["key_cache"].to(dev), c["value_cache"].to(dev), c["block_tables"].to(dev)
     cu, ctx = c["cu_query_lens"], [p[1] for p in pairs]
     whole = torch.empty(q.shape, dtype=dtype, device=dev)
-    attention_ops.multi_query_cached_kv_attention(cu, whole, q, kc, vc, c["scale"], bt, ctx, b)
     parts = torch.empty_like(whole)
-    for lo, hi in ((0, 3), (3, 6)):
-        sub_cu = [v - cu[lo] for v in cu[lo:hi + 1]]
-        attention_ops.multi_query_cached_kv_attention(sub_cu, parts[cu[lo]:cu[hi]], q[cu[lo]:cu[hi]], kc, vc, c["scale"],
-                                                      bt[lo:hi].contiguous(), ctx[lo:hi], b)
-    torch.cuda.synchronize()
+    # context splits are chosen per batch and change the order of the sums: off for the bit-for-bit comparison
+    os.environ["PA_PREFILL_SPLIT"] = "0"
+    try:
+        attention_ops.multi_query_cached_kv_attention(cu, whole, q, kc, vc, c["scale"], bt, ctx, b)
+        for lo, hi in ((0, 3), (3, 6)):
+            sub_cu = [v - cu[lo] for v in cu[lo:hi + 1]]
+            attention_ops.multi_query_cached_kv_attention(sub_cu, parts[cu[lo]:cu[hi]], q[cu[lo]:cu[hi]], kc, vc, c["scale"],
+                                                          bt[lo:hi].contiguous(), ctx[lo:hi], b)
+        torch.cuda.synchronize()
+    finally:
+        del os.environ["PA_PREFILL_SPLIT"]
     assert torch.equal(whole.view(torch.int16), parts.view(torch.int16))
     # the one-token and the 129-token chunks against the fp32 oracle
     for i in (1, 5):
         truth = paged_oracle.cached_prefill_attention_fp32([0, pairs[i][0]], c["query"][cu[i]:cu[i + 1]], c["key_cache"],
                                                            c["value_cache"], c["block_tables"][i:i + 1], [ctx[i]], c["scale"])
         _close(whole[cu[i]:cu[i + 1]].cpu(), truth, dtype, f"chunk {i}")
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("dt", ["f16", "bf16"])
+@pytest.mark.parametrize("d,b,h", [(128, 16, 8), (96, 32, 6), (64, 8, 10)])
+def test_context_splits_match_the_oracle_and_the_whole_items(dt, d, b, h):
+    """A few long items on an otherwise idle GPU are cut over their K/V tiles (plan_splits) and merged by
+    prefill_merge_kernel: the result must match the fp32 oracle and, within rounding, the same call with every item
+    kept whole; the launch counter shows that the merge kernel really ran."""
+    from vllm_b200 import _cabi
+    dtype = cases.DTYPES[dt]
+    # one-group and two-group items, contexts ending inside a page, a short sequence beside them
+    pairs = [(100, 3000 + 7), (256, 2500), (1, 2049), (40, 40)]
+    c = _random_problem(dtype, d, b, pairs, h=h, seed=d + b + h)
+    truth = paged_oracle.cached_prefill_attention_fp32(c["cu_query_lens"], c["query"], c["key_cache"], c["value_cache"],
+                                                       c["block_tables"], c["context_lens"], c["scale"])
+    before = _cabi.launch_count()
+    got = _run(c)
+    launches = _cabi.launch_count() - before
+    assert launches == 2, f"expected the prompt kernel and the merge kernel, counted {launches} launches"
+    _close(got, truth, dtype, f"split {dt} d{d} b{b}")
+    os.environ["PA_PREFILL_SPLIT"] = "0"
+    try:
+        before = _cabi.launch_count()
+        whole = _run(c)
+        assert _cabi.launch_count() - before == 1
+    finally:
+        del os.environ["PA_PREFILL_SPLIT"]
+    _close(got, whole, dtype, "split vs whole items")

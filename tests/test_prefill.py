@@ -188,13 +188,23 @@ def test_prefill_grid_order_does_not_change_results():
     qkv = torch.empty((n, 3, h, d), dtype=dtype, device="cuda").normal_(generator=g)
     scale = d ** -0.5
     whole = torch.empty((n, h, d), dtype=dtype, device="cuda")
-    attention_ops.multi_query_kv_attention(whole, qkv[:, 0], qkv[:, 1], qkv[:, 2], lens, scale)
     parts = torch.empty_like(whole)
     half = sum(lens[:4])
-    attention_ops.multi_query_kv_attention(parts[:half], qkv[:half, 0], qkv[:half, 1], qkv[:half, 2], lens[:4], scale)
-    attention_ops.multi_query_kv_attention(parts[half:], qkv[half:, 0], qkv[half:, 1], qkv[half:, 2], lens[4:], scale)
-    torch.cuda.synchronize()
+    # context splits are chosen per batch and change the order of the sums: off for the bit-for-bit comparison
+    os.environ["PA_PREFILL_SPLIT"] = "0"
+    try:
+        attention_ops.multi_query_kv_attention(whole, qkv[:, 0], qkv[:, 1], qkv[:, 2], lens, scale)
+        attention_ops.multi_query_kv_attention(parts[:half], qkv[:half, 0], qkv[:half, 1], qkv[:half, 2], lens[:4], scale)
+        attention_ops.multi_query_kv_attention(parts[half:], qkv[half:, 0], qkv[half:, 1], qkv[half:, 2], lens[4:], scale)
+        torch.cuda.synchronize()
+    finally:
+        del os.environ["PA_PREFILL_SPLIT"]
     assert torch.equal(whole.view(torch.int16), parts.view(torch.int16))
+    # and with the planner free to split (it does on this batch: 8 heads leave most of the GPU idle)
+    split = torch.empty_like(whole)
+    attention_ops.multi_query_kv_attention(split, qkv[:, 0], qkv[:, 1], qkv[:, 2], lens, scale)
+    torch.cuda.synchronize()
+    assert (split.float() - whole.float()).abs().max() <= 1e-2 * whole.float().abs().max()
     # the last prompt against the fp32 oracle (one prompt keeps the CPU side quick)
     start = n - lens[-1]
     last = qkv[start:].cpu()

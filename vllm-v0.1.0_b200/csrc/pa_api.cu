@@ -300,6 +300,8 @@ static int decode(void* out, const void* query, const void* key_cache, const voi
 
 }  // namespace pa
 
+namespace pa { void release_prefill_scratch(int dev); }   // prefill_attention.cu
+
 extern "C" {
 
 int pa_abi_version(void) { return PA_ABI_VERSION; }
@@ -311,6 +313,7 @@ int pa_release_workspaces(void) {
   int dev = 0;
   PA_CUDA_TRY(cudaGetDevice(&dev));
   PA_CUDA_TRY(cudaDeviceSynchronize());
+  pa::release_prefill_scratch(dev);
   std::lock_guard<std::mutex> lock(pa::g_ws_mu);
   for (auto it = pa::g_ws.begin(); it != pa::g_ws.end();) {
     if (it->first.first == dev) {

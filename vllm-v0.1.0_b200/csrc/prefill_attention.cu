@@ -23,8 +23,13 @@
 //   * only the diagonal tile applies the causal / length mask, tiles above it are never visited.
 // fp32 inputs take an exact SIMT path (fp32 prefill is a test-matrix case, not a serving case).
 #include <algorithm>
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
+#include <functional>
+#include <map>
 #include <mutex>
+#include <queue>
 #include <vector>
 
 #include <math_constants.h>
@@ -181,6 +186,105 @@ static int launch_tc(const CUtensorMap& mq, const CUtensorMap& mk, const CUtenso
   return check_cuda(cudaGetLastError(), "prefill_tc_kernel launch");
 }
 
+// ---------------------------------------------------------------------------
+// Context splits.  One long item on a GPU that has nothing else left to do (a short chunk behind a long cached
+// context; the last, incomplete wave of a batch of equal items) is cut over its K/V tiles into parts that run as
+// separate work items and leave (O, m, l) in a workspace; this kernel combines the parts of one 128-row group:
+// out = sum_p 2^(m_p - M) O_p / sum_p 2^(m_p - M) l_p  (the same log-sum-exp merge the decode kernel uses).
+// ---------------------------------------------------------------------------
+constexpr int kPfMaxMerge = 256;
+struct MergeTable {
+  int32_t qtok0[kPfMaxMerge];   // first query token of the sequence in the packed batch
+  int32_t qlen[kPfMaxMerge];
+  int32_t q0[kPfMaxMerge];      // first query row of the 256-row entry
+  int32_t slot0[kPfMaxMerge];   // workspace slot of (head 0, part 0); slot = slot0 + head * nparts + part
+  int32_t nparts[kPfMaxMerge];
+};
+
+// grid (head, entry, group * chunks + chunk): one CTA merges 8 columns of one 128-row group, thread = row
+template <typename T>
+__global__ void __launch_bounds__(128)
+prefill_merge_kernel(const __grid_constant__ MergeTable t, const float* __restrict__ ws, void* __restrict__ out,
+                     int64_t out_stride, int head_size, int dp) {
+  const int chunks = head_size / 8;
+  const int head = blockIdx.x, e = blockIdx.y, grp = blockIdx.z / chunks, c0 = (blockIdx.z % chunks) * 8;
+  const int r = threadIdx.x;
+  const int row = t.q0[e] + 128 * grp + r;          // row of the sequence this thread owns
+  if (t.q0[e] + 128 * grp >= t.qlen[e]) return;     // the entry has no second group
+  const int np = t.nparts[e];
+  const int64_t pf = pf_part_floats(dp);
+  const float* base = ws + (static_cast<int64_t>(t.slot0[e] + head * np) * 2 + grp) * pf;
+  float gm = -CUDART_INF_F;
+  for (int p = 0; p < np; ++p) gm = fmaxf(gm, __ldg(base + p * 2 * pf + 128 * dp + r));
+  float l = 0.f;
+  float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+  for (int p = 0; p < np; ++p) {
+    const float* pb = base + p * 2 * pf;
+    const float m = __ldg(pb + 128 * dp + r);
+    const float w = m == -CUDART_INF_F ? 0.f : ex2(m - gm);
+    l = fmaf(w, __ldg(pb + 128 * dp + 128 + r), l);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) acc[i] = fmaf(w, __ldg(pb + (c0 + i) * 128 + r), acc[i]);   // 128 contiguous bytes per warp
+  }
+  if (row < t.qlen[e]) {
+    const float inv = 1.f / l;
+    uint4 w4;
+    w4.x = pack2<T>(acc[0] * inv, acc[1] * inv); w4.y = pack2<T>(acc[2] * inv, acc[3] * inv);
+    w4.z = pack2<T>(acc[4] * inv, acc[5] * inv); w4.w = pack2<T>(acc[6] * inv, acc[7] * inv);
+    char* orow = static_cast<char*>(out) + ((static_cast<int64_t>(t.qtok0[e]) + row) * out_stride +
+                                            static_cast<int64_t>(head) * head_size) * 2;
+    *reinterpret_cast<uint4*>(orow + c0 * 2) = w4;
+  }
+}
+
+// scratch for the parts, per (device, stream) like the decode kernel's; a request that would have to grow while
+// the stream is being captured is refused (the caller then simply does not split)
+struct SplitScratch { void* ptr = nullptr; size_t bytes = 0; };
+static std::mutex g_split_mu;
+static std::map<std::pair<int, cudaStream_t>, SplitScratch> g_split_ws;
+
+static float* split_scratch(cudaStream_t stream, size_t bytes) {
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) return nullptr;
+  std::lock_guard<std::mutex> lock(g_split_mu);
+  SplitScratch& w = g_split_ws[std::make_pair(dev, stream)];
+  if (w.bytes < bytes) {
+    cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+    if (cudaStreamIsCapturing(stream, &cap) != cudaSuccess || cap != cudaStreamCaptureStatusNone) return nullptr;
+    if (w.ptr) {
+      if (cudaStreamSynchronize(stream) != cudaSuccess) return nullptr;
+      cudaFree(w.ptr);
+      w = SplitScratch();
+    }
+    const size_t want = std::max<size_t>(bytes, size_t{16} << 20);
+    if (cudaMalloc(&w.ptr, want) != cudaSuccess) { cudaGetLastError(); w = SplitScratch(); return nullptr; }
+    w.bytes = want;
+  }
+  return static_cast<float*>(w.ptr);
+}
+
+void release_prefill_scratch(int dev) {             // pa_release_workspaces
+  std::lock_guard<std::mutex> lock(g_split_mu);
+  for (auto it = g_split_ws.begin(); it != g_split_ws.end();) {
+    if (it->first.first == dev) {
+      if (it->second.ptr) cudaFree(it->second.ptr);
+      it = g_split_ws.erase(it);
+    } else {
+      ++it;
+    }
+  }
+}
+
+static int device_sms() {
+  static int sms = [] {
+    int dev = 0, n = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess)
+      n = 148;
+    return n > 0 ? n : 148;
+  }();
+  return sms;
+}
+
 // keys / values in the paged caches instead of packed rows (16-bit types)
 struct PagedKV {
   const void* key_cache;
@@ -199,6 +303,159 @@ static int launch_f32(const void* q, const void* k, const void* v, void* out, in
       static_cast<float*>(out), qs, ks, vs, os, tiles, scale_log2);
   count_launch();
   return check_cuda(cudaGetLastError(), "prefill_f32_kernel launch");
+}
+
+// One entry of the work list: 256 (16-bit) or 64 (fp32) query rows of a sequence against K/V tiles [kt0, kt1)
+struct Tile { int32_t qtok0, qlen, q0, ktok0, klen, span, kt0, kt1, slot; };
+struct MergeEntry { int32_t qtok0, qlen, q0, slot0, nparts; };
+
+// Which entries to split over their context, decided on a model of the launch: the items (entry x head) go, in
+// the grid's own order, to whichever SM is free first; an item costs its K/V tiles plus ~2 tile periods of fixed
+// work (the softmax chain filling, masked tiles, epilogue -- profiles/r2_prefill_timeline.txt; measured on 480
+// one-group items of 11 tiles: 1.84 us per tile, ~3 us per item), a part half a period more for its partial
+// result, and a launch that splits anything pays the merge kernel (~6 periods).  One knob, the same for every
+// entry: the longest part allowed, g tiles; an entry longer than g is cut into equal parts of at most g.  The g with
+// the shortest modelled makespan wins if it beats the unsplit launch by 6 %.  Large launches balance themselves
+// and are left alone.  Returns the workspace (nullptr: nothing is split); entries of *all are replaced by their
+// parts, re-sorted.
+static float* plan_splits(std::vector<Tile>* all, std::vector<MergeEntry>* merges, int num_heads, int dp,
+                          bool tile_major, cudaStream_t stream) {
+  // read per call (tests switch it): PA_PREFILL_SPLIT=0 keeps every entry whole
+  const char* env = getenv("PA_PREFILL_SPLIT");
+  const bool off = env && env[0] == '0';
+  static const bool verbose = [] { const char* e = getenv("PA_PREFILL_SPLIT_DEBUG"); return e && e[0] == '1'; }();
+  const int sms = device_sms();
+  const size_t n = all->size();
+  if (off || n * num_heads > static_cast<size_t>(8 * sms) || n > 512) return nullptr;
+  constexpr double kFixed = 2.0, kPartExtra = 0.5, kMerge = 6.0;   // in K/V tile periods
+  constexpr int kMinPart = 3;                       // tiles
+  struct Ent { int nfull, first_diag, parts; };
+  std::vector<Ent> ents(n);
+  int longest = 0;
+  for (size_t i = 0; i < n; ++i) {
+    const Tile& t = (*all)[i];
+    const int koff = t.klen - t.qlen;
+    const int last_row = std::min(t.q0 + kPfRows, t.qlen) - 1;
+    ents[i].nfull = std::min(last_row + koff, t.klen - 1) / kPfCols + 1;
+    ents[i].first_diag = (t.q0 + koff) / kPfCols;   // the last part must start at or before this tile
+    ents[i].parts = 1;
+    longest = std::max(longest, ents[i].nfull);
+  }
+  // part boundaries of an entry cut into k parts: the last part starts at `last`, the others share [0, last) evenly
+  auto last_start = [&](const Ent& e, int k) { return std::min(e.first_diag, (k - 1) * e.nfull / k); };
+  auto can_split = [&](const Ent& e, int k) {
+    if (k > 64) return false;
+    const int last = last_start(e, k);
+    return last / (k - 1) >= kMinPart && e.nfull - last >= kMinPart;
+  };
+  auto part_begin = [&](const Ent& e, int k, int i) { return k == 1 ? 0 : (i == k - 1 ? last_start(e, k) : i * last_start(e, k) / (k - 1)); };
+  if (longest < 2 * kMinPart) return nullptr;       // nothing to decide for batches of short prompts
+  // Modelled makespan of the current ents[].parts, items dispatched in the grid's order.  Costs are counted in half
+  // periods; the SMs' free times are kept as a short ascending list of (time, SMs) and every run of equal-cost
+  // items is handed out as a batch, so one evaluation costs a few hundred list operations, not one heap operation
+  // per item.
+  std::vector<int> costs;
+  std::vector<std::pair<int, int>> runs, sm;       // (cost, items), (free at, SMs)
+  auto simulate = [&]() {
+    costs.clear();
+    bool any = false;
+    for (size_t i = 0; i < n; ++i)
+      for (int k = 0; k < ents[i].parts; ++k) {
+        const int b = part_begin(ents[i], ents[i].parts, k);
+        const int e = k + 1 < ents[i].parts ? part_begin(ents[i], ents[i].parts, k + 1) : ents[i].nfull;
+        costs.push_back(2 * (e - b) + static_cast<int>(2 * kFixed) + (ents[i].parts > 1 ? static_cast<int>(2 * kPartExtra) : 0));
+        any |= ents[i].parts > 1;
+      }
+    std::sort(costs.begin(), costs.end(), std::greater<int>());   // the launch sorts by span
+    runs.clear();
+    for (int c : costs) {
+      if (!runs.empty() && runs.back().first == c) ++runs.back().second;
+      else runs.emplace_back(c, 1);
+    }
+    sm.assign(1, std::make_pair(0, sms));
+    int makespan = 0;
+    auto put = [&](int c, int m) {
+      while (m > 0) {
+        const int t = sm.front().first, x = std::min(sm.front().second, m);
+        if (x == sm.front().second) sm.erase(sm.begin());
+        else sm.front().second -= x;
+        const int nt = t + c;
+        makespan = std::max(makespan, nt);
+        auto it = sm.end();
+        while (it != sm.begin() && (it - 1)->first > nt) --it;
+        if (it != sm.begin() && (it - 1)->first == nt) (it - 1)->second += x;
+        else sm.insert(it, std::make_pair(nt, x));
+        m -= x;
+      }
+    };
+    if (tile_major) {
+      for (int h = 0; h < num_heads; ++h)
+        for (const auto& r : runs) put(r.first, r.second);
+    } else {
+      for (const auto& r : runs) put(r.first, r.second * num_heads);
+    }
+    return 0.5 * makespan + (any ? kMerge : 0.0);
+  };
+  const double unsplit = simulate();
+  double best = unsplit;
+  int best_g = 0;
+  static const int kCuts[] = {2, 3, 4, 6, 8, 12, 16, 24};
+  int prev_g = 0, worse = 0;
+  for (int cut : kCuts) {
+    const int g = std::max((longest + cut - 1) / cut, kMinPart);
+    if (g == prev_g) continue;
+    prev_g = g;
+    size_t pieces = 0;
+    for (size_t i = 0; i < n; ++i) {
+      int k = (ents[i].nfull + g - 1) / g;
+      while (k > 1 && !can_split(ents[i], k)) --k;
+      ents[i].parts = k;
+      pieces += k;
+    }
+    if (pieces * num_heads > static_cast<size_t>(24 * sms) || pieces > kPfMaxTiles) break;
+    const double m = simulate();
+    if (m < best) { best = m; best_g = g; worse = 0; }
+    else if (++worse == 2) break;                  // finer parts only add fixed costs from here on
+  }
+  if (best_g == 0 || best > 0.94 * unsplit) return nullptr;
+  int64_t slots = 0;
+  for (size_t i = 0; i < n; ++i) {
+    int k = (ents[i].nfull + best_g - 1) / best_g;
+    while (k > 1 && !can_split(ents[i], k)) --k;
+    ents[i].parts = k;
+    if (k > 1) slots += static_cast<int64_t>(k) * num_heads;
+  }
+  const int64_t bytes = slots * 2 * pf_part_floats(dp) * 4;
+  if (slots == 0 || slots >= (1 << 23) || bytes > (int64_t{1} << 30)) return nullptr;
+  float* ws = split_scratch(stream, static_cast<size_t>(bytes));
+  if (!ws && !verbose) return nullptr;
+  std::vector<Tile> out;
+  int32_t slot0 = 0;
+  for (size_t i = 0; i < n; ++i) {
+    const Tile& t = (*all)[i];
+    const int k = ents[i].parts;
+    if (k == 1) { out.push_back(t); continue; }
+    for (int j = 0; j < k; ++j) {
+      Tile pt = t;
+      pt.kt0 = part_begin(ents[i], k, j);
+      pt.kt1 = j + 1 < k ? part_begin(ents[i], k, j + 1) : 0xffff;
+      pt.span = (std::min(pt.kt1, ents[i].nfull) - pt.kt0) * kPfCols;
+      pt.slot = ((slot0 + j) << 8) | k;
+      out.push_back(pt);
+    }
+    merges->push_back({t.qtok0, t.qlen, t.q0, slot0, k});
+    slot0 += k * num_heads;
+  }
+  std::stable_sort(out.begin(), out.end(), [](const Tile& a, const Tile& b) { return a.span > b.span; });
+  if (verbose) {
+    fprintf(stderr, "[plan_splits] %zu entries x %d heads -> %zu (parts of at most %d tiles), modelled makespan %.1f vs %.1f unsplit:",
+            n, num_heads, out.size(), best_g, best, unsplit);
+    for (const Tile& t : out) fprintf(stderr, " q0=%d[%d,%d)%s", t.q0, t.kt0, t.kt1 == 0xffff ? -1 : t.kt1, t.slot < 0 ? "" : "*");
+    fprintf(stderr, "\n");
+  }
+  if (!ws) { merges->clear(); return nullptr; }     // planner debugging without a GPU
+  all->swap(out);
+  return ws;
 }
 
 // key_lens == nullptr: plain prompt attention (every sequence's keys are its own query tokens' keys).
@@ -223,7 +480,6 @@ static int prefill(void* out, const void* query, const void* key, const void* va
 
   // tiles: one per 256 (16-bit) or 64 (fp32) query rows of a sequence; longest K/V span first
   const int rows = dtype == PA_F32 ? 64 : kPfRows;
-  struct Tile { int32_t qtok0, qlen, q0, ktok0, klen, span; };
   std::vector<Tile> all;
   int64_t tok = 0, ktok = 0;
   for (int i = 0; i < num_seqs; ++i) {
@@ -234,12 +490,17 @@ static int prefill(void* out, const void* query, const void* key, const void* va
     if (tok + len > 0x7fffffff || ktok + klen > 0x7fffffff) return set_error(PA_ERR_INVALID_ARGUMENT, "too many tokens");
     for (int32_t q0 = 0; q0 < len; q0 += rows)
       all.push_back({static_cast<int32_t>(tok), len, q0, paged ? i : static_cast<int32_t>(ktok), klen,
-                     std::min(q0 + rows + (klen - len), klen)});
+                     std::min(q0 + rows + (klen - len), klen), 0, 0xffff, -1});
     tok += len;
     ktok += klen;
   }
   if (all.empty()) return PA_OK;
   std::stable_sort(all.begin(), all.end(), [](const Tile& a, const Tile& b) { return a.span > b.span; });
+  float* split_ws = nullptr;
+  std::vector<MergeEntry> merges;
+  // K/V bytes of the batch against the L2 (126 MB on B200): beyond it, query tiles of one head run together
+  const bool tile_major = ktok * num_heads * head_size * 4 > (int64_t{96} << 20);
+  if (dtype != PA_F32) split_ws = plan_splits(&all, &merges, num_heads, head_size <= 64 ? 64 : 128, tile_major, stream);
 
   CUtensorMap mq, mk, mv, mo;
   const int dp = head_size <= 64 ? 64 : 128;
@@ -255,8 +516,8 @@ static int prefill(void* out, const void* query, const void* key, const void* va
   PrefillParams p;
   p.out = out; p.out_stride = out_stride; p.num_heads = num_heads; p.head_size = head_size;
   p.scale_log2 = scale * 1.4426950408889634f; p.dbg = dbg;
-  // K/V bytes of the batch against the L2 (126 MB on B200): beyond it, query tiles of one head run together
-  p.tile_major = ktok * num_heads * head_size * 4 > (int64_t{96} << 20);
+  p.tile_major = tile_major;
+  p.split_ws = split_ws;
   p.key_cache = nullptr; p.value_cache = nullptr; p.block_tables = nullptr; p.max_blocks = 0; p.block_shift = 0;
   if (paged) {
     p.key_cache = paged->key_cache; p.value_cache = paged->value_cache; p.block_tables = paged->block_tables;
@@ -270,6 +531,7 @@ static int prefill(void* out, const void* query, const void* key, const void* va
     for (int i = 0; i < n; ++i) {
       const Tile& t = all[begin + i];
       tiles.qtok0[i] = t.qtok0; tiles.qlen[i] = t.qlen; tiles.q0[i] = t.q0; tiles.ktok0[i] = t.ktok0; tiles.klen[i] = t.klen;
+      tiles.krange[i] = t.kt0 | (t.kt1 << 16); tiles.slot[i] = t.slot;
     }
     int rc;
     if (dtype == PA_F32) {
@@ -289,6 +551,23 @@ static int prefill(void* out, const void* query, const void* key, const void* va
     }
     if (rc != PA_OK) return rc;
     p.dbg = nullptr;
+  }
+  // the parts of split entries -> out
+  static thread_local MergeTable mt;
+  for (size_t begin = 0; begin < merges.size(); begin += kPfMaxMerge) {
+    const int n = static_cast<int>(std::min<size_t>(kPfMaxMerge, merges.size() - begin));
+    bool second_group = false;
+    for (int i = 0; i < n; ++i) {
+      const MergeEntry& m = merges[begin + i];
+      mt.qtok0[i] = m.qtok0; mt.qlen[i] = m.qlen; mt.q0[i] = m.q0; mt.slot0[i] = m.slot0; mt.nparts[i] = m.nparts;
+      second_group |= m.q0 + 128 < m.qlen;
+    }
+    const dim3 grid(num_heads, n, (second_group ? 2 : 1) * (head_size / 8));
+    if (dtype == PA_F16) prefill_merge_kernel<F16><<<grid, 128, 0, stream>>>(mt, split_ws, out, out_stride, head_size, dp);
+    else prefill_merge_kernel<BF16><<<grid, 128, 0, stream>>>(mt, split_ws, out, out_stride, head_size, dp);
+    count_launch();
+    const int rc = check_cuda(cudaGetLastError(), "prefill_merge_kernel launch");
+    if (rc != PA_OK) return rc;
   }
   return PA_OK;
 }

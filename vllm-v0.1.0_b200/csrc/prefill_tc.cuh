@@ -42,7 +42,18 @@ struct PrefillTiles {
   int32_t q0[kPfMaxTiles];     // first query row of this CTA inside the sequence (multiple of its row count)
   int32_t ktok0[kPfMaxTiles];  // first key token of the sequence in the packed keys / values
   int32_t klen[kPfMaxTiles];   // keys of the sequence
+  // Context splits: an entry may cover only K/V tiles [kt0, kt1) of its query tile (kt0 | kt1 << 16; 0 | 0xffff =
+  // everything).  Such an entry leaves un-normalised partial results in the workspace slot (slot >> 8) +
+  // head * (slot & 255) instead of writing out (slot < 0: a whole item); prefill_merge_kernel combines them.
+  // Every part starts at or before the tile that holds the last key of the entry's FIRST row, so each of its rows
+  // sees at least one key in the part's first tile (the masked tiles all belong to the last part).
+  int32_t krange[kPfMaxTiles];
+  int32_t slot[kPfMaxTiles];
 };
+
+// floats per (slot, 128-row group) of the split workspace: O transposed [DP][128] (a warp's stores of one column
+// are 128 contiguous bytes), then the rows' running maxima (exp2 domain) and sums
+__host__ __device__ constexpr int64_t pf_part_floats(int dp) { return static_cast<int64_t>(128) * dp + 256; }
 
 struct PrefillParams {
   void* out;
@@ -61,6 +72,7 @@ struct PrefillParams {
   // 1: grid (tile, head) -- for batches whose K/V exceeds L2.  Measured on B200: 8 x 4096 tokens 948 -> 1064
   // TFLOP/s with 1, 5 x 512 tokens 317 -> 304 and a ragged 2560-token batch 418 -> 360 with it.
   int32_t tile_major;
+  float* split_ws;              // partial results of split entries (see PrefillTiles::slot)
 };
 
 // tests / tools: SM-clock stamps of the hand-offs of CTA (head 0, tile 0) into the debug buffer, after the raw
@@ -155,7 +167,7 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant
   // grid order (host's choice, see PrefillParams::tile_major): tiles fastest keeps the CTAs that run together on
   // few heads, so a head's K/V is read from HBM once and from L2 by its other query tiles
   struct Item {
-    int head, tile, qtok0, qlen, q0, ktok0, klen, koff, nA, nB, nmax;
+    int head, tile, qtok0, qlen, q0, ktok0, klen, koff, nA, nB, nmax, kt0, slot;
   };
   auto decode = [&](int bx, int by) {
     Item it;
@@ -166,9 +178,14 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant
     it.koff = it.klen - it.qlen;                  // keys in front of the first query row
     // K/V tiles each query tile visits: everything up to and including the tile that holds the last key its
     // last row sees (plain prompts: its diagonal tile).  nB is nA or nA + 1.
-    it.nA = min(it.q0 + 127 + it.koff, it.klen - 1) / kPfCols + 1;
-    it.nB = (it.q0 + 128 < it.qlen) ? min(it.q0 + 255 + it.koff, it.klen - 1) / kPfCols + 1 : 0;
+    const uint32_t kr = static_cast<uint32_t>(tiles.krange[it.tile]);
+    const int kt1 = static_cast<int>(kr >> 16);
+    it.kt0 = static_cast<int>(kr & 0xffffu);
+    it.nA = min(min(it.q0 + 127 + it.koff, it.klen - 1) / kPfCols + 1, kt1) - it.kt0;
+    it.nB = (it.q0 + 128 < it.qlen) ? min(min(it.q0 + 255 + it.koff, it.klen - 1) / kPfCols + 1, kt1) - it.kt0 : 0;
     it.nmax = it.nB > it.nA ? it.nB : it.nA;
+    const int si = tiles.slot[it.tile];
+    it.slot = si < 0 ? -1 : (si >> 8) + it.head * (si & 255);
     return it;
   };
   // Item n + 1 of this CTA is the answer to the n-th request (slot n & 1), issued by the scheduler thread when
@@ -268,13 +285,13 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant
       __syncwarp();
       table = p.block_tables + static_cast<int64_t>(it.ktok0) * p.max_blocks;   // ktok0 = sequence index
       klen = it.klen;
-      int next_blocks = tile_blocks(0);
+      int next_blocks = tile_blocks(it.kt0);
       for (int j = 0; j < it.nmax; ++j, ++g) {
         const int s = g & 1;
         const uint32_t ph = ((g >> 1) & 1) ^ 1;     // first use of a stage passes immediately
         const int blocks = next_blocks;
-        if (j + 1 < it.nmax) next_blocks = tile_blocks(j + 1);
-        const int nvalid = min(klen - j * kPfCols, kPfCols);   // tokens of this tile inside the context (>= 1)
+        if (j + 1 < it.nmax) next_blocks = tile_blocks(it.kt0 + j + 1);
+        const int nvalid = min(klen - (it.kt0 + j) * kPfCols, kPfCols);   // tokens of this tile inside the context (>= 1)
         const int ngrp = (nvalid + 7) >> 3, npages = (nvalid + B - 1) >> shB;
         const int row = blocks * H + it.head;       // lane l: (block, head) row of page l in both caches
         mbar_wait(bar_ke + 8 * s, ph);
@@ -354,7 +371,7 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant
           const uint32_t ph = ((g >> 1) & 1) ^ 1;  // first use of a stage passes immediately
           mbar_wait(bar_ke + 8 * s, ph);
           mbar_expect_tx(bar_kf + 8 * s, kTileBytes);
-          load_tile(&tmk, sK + s * kTileBytes, it.ktok0 + j * kPfCols, bar_kf + 8 * s);
+          load_tile(&tmk, sK + s * kTileBytes, it.ktok0 + (it.kt0 + j) * kPfCols, bar_kf + 8 * s);
           if (j == 0 && it.nB) {
             if (cB > 0) mbar_wait(bar_qe1, (cB - 1) & 1);
             mbar_expect_tx(bar_q1, kTileBytes);
@@ -363,7 +380,7 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant
           }
           mbar_wait(bar_ve + 8 * s, ph);
           mbar_expect_tx(bar_vf + 8 * s, kTileBytes);
-          load_tile(&tmv, sV + s * kTileBytes, it.ktok0 + j * kPfCols, bar_vf + 8 * s);
+          load_tile(&tmv, sV + s * kTileBytes, it.ktok0 + (it.kt0 + j) * kPfCols, bar_vf + 8 * s);
         }
         if (!next_item(n, it, true)) break;
       }
@@ -435,7 +452,7 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant
         const int g = g0 + j, s = g & 1;
         const bool more_k = j + 1 < nmax;
         mbar_wait(bar_vf + 8 * s, (g >> 1) & 1);
-        const int kmax = kPaged ? (min(it.klen - j * kPfCols, kPfCols) + 15) >> 4 : kPfCols / 16;
+        const int kmax = kPaged ? (min(it.klen - (it.kt0 + j) * kPfCols, kPfCols) + 15) >> 4 : kPfCols / 16;
         stamp(p.dbg, tl, 2, g, 4);
 #pragma unroll
         for (int i = 0; i < 2; ++i) {
@@ -505,7 +522,8 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant
     for (int n = 0;; ++n) {
       const int nA = it.nA, nB = it.nB;
       const int ni = grp ? nB : nA;
-      const int head = it.head, qtok0 = it.qtok0, qlen = it.qlen, klen = it.klen, koff = it.koff;
+      const int head = it.head, qtok0 = it.qtok0, qlen = it.qlen, klen = it.klen, koff = it.koff, kt0 = it.kt0;
+      const int slot = it.slot;
       const int qi0 = it.q0 + 128 * grp;            // first row of this tile inside the prompt
       const bool dump = p.dbg && head == 0 && it.tile == 0 && grp == 0;
       const bool tl = p.dbg && blockIdx.x == 0 && blockIdx.y == 0 && r == 0;
@@ -536,8 +554,8 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant
         // only tiles reaching past the last key of the tile's FIRST row need masking: the diagonal tile of a
         // plain prompt, at most the last two tiles when cached keys shift the diagonal off the tile grid.
         // A row wholly masked in such a tile (never tile 0) keeps its running maximum: all its p are 0.
-        if ((j + 1) * kPfCols - 1 > min(qi0 + koff, klen - 1)) {
-          const int lim = min(qi0 + r + koff, klen - 1) - j * kPfCols;   // last valid column of this row
+        if ((kt0 + j + 1) * kPfCols - 1 > min(qi0 + koff, klen - 1)) {
+          const int lim = min(qi0 + r + koff, klen - 1) - (kt0 + j) * kPfCols;   // last valid column of this row
 #pragma unroll
           for (int c = 0; c < 4; ++c)
 #pragma unroll
@@ -630,6 +648,21 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant
         ++co;
         tc05::fence_after_sync();
         stamp(p.dbg, tl, grp, cs - 1, 6);             // O ready (the item's last P.V has run)
+        if (slot >= 0) {
+          // one part of a split context: O as it stands (relative to m_run, not normalised), m_run and l_run go to
+          // the workspace; column-major, so that the 32 rows of a warp store 128 contiguous bytes per column
+          float* ws = p.split_ws + (static_cast<int64_t>(slot) * 2 + grp) * pf_part_floats(DP);
+#pragma unroll
+          for (int c = 0; c < DP / 32; ++c) {
+            uint32_t o[32];
+            tc05::tmem_ld32(tO + c * 32, o);
+            tc05::tmem_wait_ld();
+#pragma unroll
+            for (int i = 0; i < 32; ++i) ws[(c * 32 + i) * 128 + r] = __uint_as_float(o[i]);
+          }
+          ws[128 * DP + r] = m_run;
+          ws[128 * DP + 128 + r] = l_run;
+        } else {
         const int D = p.head_size;
         const float inv = 1.f / l_run;
         named_sync_n(3 + grp, 128);                   // row 0's thread has seen the buffer released
@@ -678,6 +711,7 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant
             *reinterpret_cast<uint4*>(obase + static_cast<int64_t>(row) * p.out_stride * 2 + chunk * 16) = w;
           }
           named_sync_n(3 + grp, 128);                 // everybody has read its chunks
+        }
         }
       }
       if (r == 0) mbar_arrive(bar_stg);
