@@ -15,9 +15,9 @@
  *     synchronising the host;
  *   - every function returns PA_OK (0) or a negative PA_ERR_* code;
  *     pa_last_error() then returns a thread-local, NUL-terminated message;
- *   - the caller owns every buffer.  The only state kept by the library is a
- *     per-(device, stream) scratch buffer for split-context partial results
- *     (see pa_release_workspaces).
+ *   - the caller owns every buffer.  The only state kept by the library is
+ *     per-(device, stream) scratch for split-context partial results of the
+ *     decode and the prompt kernels (see pa_release_workspaces).
  *
  * Data layout (reference: vllm/worker/cache_engine.py:48-63,
  * csrc/cache_kernels.cu:165-178), with x = 16 / sizeof(T):
@@ -238,10 +238,14 @@ PA_API int pa_prefill_attention_debug(void* out, const void* query, const void* 
  * (DEVICE, int32 [num_seqs][max_num_blocks_per_seq]) as for pa_decode_attention.
  * query_lens and context_lens are HOST arrays (the reference keeps cu_query_lens as a
  * Python list).  head_size in {64, 80, 96, 128}, block_size in {8, 16, 32}.
- * PA_F16 / PA_BF16: ONE launch -- the tcgen05 prompt kernel's producer warps copy the pages
- * themselves (cp.async, 16-byte chunks placed where the 128-byte swizzle of the operand tile
- * wants them; tokens past the context zero-filled); no scratch: workspace may be NULL,
- * pa_multi_query_cached_kv_workspace_bytes returns 0.
+ * PA_F16 / PA_BF16: the tcgen05 prompt kernel reads the pages itself -- a producer warp issues
+ * TMA loads through tensor maps over the caches (a K page is a set of no-swizzle core matrices,
+ * a V page a K-major operand under 32- / 64-byte swizzle); tokens past the context are zeroed in
+ * shared memory.  No caller scratch: workspace may be NULL and
+ * pa_multi_query_cached_kv_workspace_bytes returns 0.  One launch, or two when long items of a
+ * small batch are split over their context (parts + a merge kernel; the partial results live in
+ * the library's own per-(device, stream) scratch, see pa_release_workspaces; PA_PREFILL_SPLIT=0
+ * in the environment, read per call, keeps every item whole and the summation order fixed).
  * PA_F32 (a test-matrix case): slot generation + page gather into `workspace` (DEVICE scratch,
  * 256-byte aligned, at least pa_multi_query_cached_kv_workspace_bytes(sum(context_lens), ...)
  * bytes, owned by the caller, free for reuse once the stream has passed this call) + the exact
