@@ -117,7 +117,12 @@ PA_API int pa_stream_read_probe(const void* src, int64_t bytes, int32_t ctas_per
  *   block_tables   [num_seqs][max_num_blocks_per_seq]        int32
  *   context_lens   [num_seqs]                                int32
  *   max_context_len upper bound of context_lens (sizes the split-context
- *                  schedule only; the reference used it to size shared memory)
+ *                  schedule; the reference used it to size shared memory).
+ *                  REQUIRED: max_context_len >= max(context_lens), as
+ *                  worker.py:191 computes it.  The page walk is capped by the
+ *                  schedule derived from it, so a sequence longer than
+ *                  max_context_len would lose its tail tokens without an error
+ *                  (context_lens lives on the device; the host cannot check).
  *
  * head_size in {64, 80, 96, 128}, block_size in {8, 16, 32}, any pa_dtype --
  * the reference's dispatch set (attention_kernels.cu:370-400, 416-448,
