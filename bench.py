@@ -685,6 +685,70 @@ def prefill_block(dev):
     return rows
 
 
+def cached_prefill_block(dev):
+    """Prompt chunks over the paged cache (pa_multi_query_cached_kv_attention: tcgen05 kernel fed by TMA straight from
+    the cache pages, long items split over their context) beside what v0.1.0 has to do without the operator --
+    recompute the whole prompt.  The last query row of every sequence sees its whole context, so it must agree with
+    the decode kernel on the same cache (checked on every shape)."""
+    import torch
+    from vllm_b200 import attention_ops
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            peak = float(json.load(f)["bf16_tflops"])
+    except Exception:
+        peak = 1590.0
+    shapes = (("llama13b_chunk512_of_2048_x8", 40, 128, 16, [(512, 2048)] * 8, torch.bfloat16),
+              ("llama13b_chunk2048_of_8192_x4", 40, 128, 16, [(2048, 8192)] * 4, torch.bfloat16),
+              ("llama7b_fp16_ragged", 32, 128, 16, [(37, 1500), (911, 911), (128, 4096), (460, 600)], torch.float16))
+    rows = []
+    for name, h, d, b, pairs, dtype in shapes:
+        ctx, qlens = [p[1] for p in pairs], [p[0] for p in pairs]
+        cu = [0]
+        for n in qlens:
+            cu.append(cu[-1] + n)
+        nblocks = sum((c + b - 1) // b for c in ctx)
+        g = torch.Generator(device=dev).manual_seed(0)
+        kc = torch.empty((nblocks, h, d // 8, b, 8), dtype=dtype, device=dev).normal_(generator=g)
+        vc = torch.empty((nblocks, h, d, b), dtype=dtype, device=dev).normal_(generator=g)
+        q = torch.empty((cu[-1], h, d), dtype=dtype, device=dev).normal_(generator=g)
+        out = torch.empty_like(q)
+        mb = max((c + b - 1) // b for c in ctx)
+        bt = torch.zeros((len(pairs), mb), dtype=torch.int32)
+        perm = torch.randperm(nblocks, generator=torch.Generator().manual_seed(1)).int()
+        at = 0
+        for i, c in enumerate(ctx):
+            n = (c + b - 1) // b
+            bt[i, :n] = perm[at:at + n]
+            at += n
+        btd = bt.to(dev)
+        scale = d ** -0.5
+        call = lambda: attention_ops.multi_query_cached_kv_attention(cu, out, q, kc, vc, scale, btd, ctx, b)
+        ms = _time_events(call, iters=20, warm=5)
+        fl = sum(4 * d * h * sum(min(c, r + 1 + c - n) for r in range(n)) for n, c in pairs)
+        # the last row of each chunk against the decode kernel
+        last = torch.tensor([cu[i + 1] - 1 for i in range(len(pairs))], device=dev)
+        dec = torch.empty((len(pairs), h, d), dtype=dtype, device=dev)
+        attention_ops.single_query_cached_kv_attention(dec, q[last].contiguous(), kc, vc, scale, btd,
+                                                       torch.tensor(ctx, dtype=torch.int32, device=dev), b, max(ctx))
+        torch.cuda.synchronize()
+        err = float((out[last].float() - dec.float()).abs().max())
+        tol = (1e-2 if dtype == torch.bfloat16 else 1e-3) * max(1.0, float(dec.float().abs().max()))
+        qf = torch.empty((sum(ctx), 3, h, d), dtype=dtype, device=dev).normal_(generator=g)
+        of = torch.empty((sum(ctx), h, d), dtype=dtype, device=dev)
+        ms_full = _time_events(lambda: attention_ops.multi_query_kv_attention(of, qf[:, 0], qf[:, 1], qf[:, 2], ctx, scale),
+                               iters=10, warm=3)
+        rows.append({"shape": name, "heads": h, "head_size": d, "block_size": b,
+                     "query_and_context_lens": pairs if len(set(pairs)) > 1 else [list(pairs[0]), len(pairs)],
+                     "dtype": str(dtype).split(".")[-1], "ms": ms,
+                     "roofline": {"bound": "tensor", "achieved": fl / ms / 1e9, "peak": peak, "unit": "TFLOP/s",
+                                  "frac": fl / ms / 1e9 / peak, "traffic": None, "algorithmic_flops_per_launch": fl},
+                     "recompute_whole_prompt_ms": ms_full, "speedup_vs_recompute": ms_full / ms,
+                     "last_rows_vs_decode_kernel": {"max_abs_diff": err, "tolerance": tol, "ok": err <= tol}})
+        del kc, vc, q, out, qf, of
+        torch.cuda.empty_cache()
+    return rows
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -807,13 +871,14 @@ def main():
             print(f"[bench] {fn.__name__} failed: {e!r}", file=sys.stderr)
             return {"error": repr(e)[:300]}
 
-    also = movers = prefill = ref_kernel = allreduce = None
+    also = movers = prefill = cached_prefill = ref_kernel = allreduce = None
     extras = args.workload == "llama13b_tp" and not args.no_also
     if extras and n_gpus == 1:
         k2 = min(args.steps, 100)
         also = [guarded(decode_block, name, dev, k2, args.warmup, peak) for name in ("llama7b", "neox20b_tp8", "opt66b_tp8")]
         movers = guarded(movers_block, dev, peak)
         prefill = guarded(prefill_block, dev)
+        cached_prefill = guarded(cached_prefill_block, dev)
         # config 3 at one GPU is out of the reference kernel's reach (32-bit offsets): configs[1] stands in
         ref_kernel = gpu_reference_kernel("llama7b", WORKLOADS["llama7b"]["heads"], local)
     elif extras:
@@ -879,6 +944,8 @@ def main():
             line["cache_movers"] = movers
         if prefill is not None:
             line["prefill"] = prefill
+        if cached_prefill is not None:
+            line["cached_prefill"] = cached_prefill
         if allreduce is not None:
             line["allreduce"] = allreduce
         print(json.dumps(line), flush=True)
