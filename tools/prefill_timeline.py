@@ -13,7 +13,7 @@ from vllm_b200 import attention_ops  # noqa: E402
 
 L = int(sys.argv[1]) if len(sys.argv) > 1 else 4096
 nprompts = int(sys.argv[2]) if len(sys.argv) > 2 else 8
-h, d, lens = int(os.environ.get("PF_HEADS", "40")), 128, [L] * nprompts
+h, d, lens = int(os.environ.get("PF_HEADS", "40")), int(os.environ.get("PF_HEAD_SIZE", "128")), [L] * nprompts
 dd = d
 n = sum(lens)
 qkv = torch.empty((n, 3, h, d), dtype=torch.bfloat16, device="cuda").normal_()
