@@ -174,16 +174,28 @@ static int make_page_maps(CUtensorMap* mk, CUtensorMap* mv, const void* key_cach
   return PA_OK;
 }
 
-template <typename T, int DP, bool kPaged>
-static int launch_tc(const CUtensorMap& mq, const CUtensorMap& mk, const CUtensorMap& mv, const CUtensorMap& mo,
-                     const PrefillTiles& tiles,
-                     int ntiles, const PrefillParams& p, cudaStream_t stream) {
+template <typename T, int DP, bool kPaged, int kTiles>
+static int launch_tc_n(const CUtensorMap& mq, const CUtensorMap& mk, const CUtensorMap& mv, const CUtensorMap& mo,
+                       const PrefillTilesT<kTiles>& tiles, int ntiles, const PrefillParams& p, cudaStream_t stream) {
   constexpr int smem = 7 * (DP / 64) * 128 * 128 + 1024 + 256;   // Q x 2, K x 2, V x 2, output staging; alignment slack; barriers
-  auto kern = prefill_tc_kernel<T, DP, kPaged>;
+  auto kern = prefill_tc_kernel<T, DP, kPaged, kTiles>;
   PA_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
   kern<<<p.tile_major ? dim3(ntiles, p.num_heads) : dim3(p.num_heads, ntiles), kPfThreads, smem, stream>>>(mq, mk, mv, mo, tiles, p);
   count_launch();
   return check_cuda(cudaGetLastError(), "prefill_tc_kernel launch");
+}
+
+// up to kPfFewTiles entries travel in the small table (see PrefillTilesT)
+template <typename T, int DP, bool kPaged>
+static int launch_tc(const CUtensorMap& mq, const CUtensorMap& mk, const CUtensorMap& mv, const CUtensorMap& mo,
+                     const PrefillTiles& tiles, int ntiles, const PrefillParams& p, cudaStream_t stream) {
+  if (ntiles > kPfFewTiles) return launch_tc_n<T, DP, kPaged, kPfMaxTiles>(mq, mk, mv, mo, tiles, ntiles, p, stream);
+  PrefillTilesT<kPfFewTiles> few;
+  for (int i = 0; i < ntiles; ++i) {
+    few.qtok0[i] = tiles.qtok0[i]; few.qlen[i] = tiles.qlen[i]; few.q0[i] = tiles.q0[i]; few.ktok0[i] = tiles.ktok0[i];
+    few.klen[i] = tiles.klen[i]; few.krange[i] = tiles.krange[i]; few.slot[i] = tiles.slot[i];
+  }
+  return launch_tc_n<T, DP, kPaged, kPfFewTiles>(mq, mk, mv, mo, few, ntiles, p, stream);
 }
 
 // ---------------------------------------------------------------------------

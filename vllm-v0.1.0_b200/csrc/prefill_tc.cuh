@@ -36,20 +36,26 @@ constexpr int kPfThreads = 384;   // 8 softmax warps + producer + issuer + 2 idl
 // A sequence has qlen query rows (packed from token qtok0 of q / out) and klen >= qlen keys (packed from
 // token ktok0 of k / v).  Query row i sees keys 0 .. i + (klen - qlen): plain prompt attention is
 // klen == qlen; klen > qlen is a prompt chunk behind klen - qlen tokens that are already cached.
-struct PrefillTiles {
-  int32_t qtok0[kPfMaxTiles];  // first query token of the sequence in the packed batch
-  int32_t qlen[kPfMaxTiles];   // query rows of the sequence
-  int32_t q0[kPfMaxTiles];     // first query row of this CTA inside the sequence (multiple of its row count)
-  int32_t ktok0[kPfMaxTiles];  // first key token of the sequence in the packed keys / values
-  int32_t klen[kPfMaxTiles];   // keys of the sequence
+// The table travels as a kernel parameter, and parameters cost launch time (measured: 5 x 512 tokens, eager
+// back-to-back launches, 36.7 us per call with a 20 KB table, 41.5 us with 28 KB, the kernel itself 32-33 us), so
+// launches of up to kPfFewTiles entries use the small instantiation (1.8 KB).
+constexpr int kPfFewTiles = 64;
+template <int N>
+struct PrefillTilesT {
+  int32_t qtok0[N];            // first query token of the sequence in the packed batch
+  int32_t qlen[N];             // query rows of the sequence
+  int32_t q0[N];               // first query row of this CTA inside the sequence (multiple of its row count)
+  int32_t ktok0[N];            // first key token of the sequence in the packed keys / values
+  int32_t klen[N];             // keys of the sequence
   // Context splits: an entry may cover only K/V tiles [kt0, kt1) of its query tile (kt0 | kt1 << 16; 0 | 0xffff =
   // everything).  Such an entry leaves un-normalised partial results in the workspace slot (slot >> 8) +
   // head * (slot & 255) instead of writing out (slot < 0: a whole item); prefill_merge_kernel combines them.
   // Every part starts at or before the tile that holds the last key of the entry's FIRST row, so each of its rows
   // sees at least one key in the part's first tile (the masked tiles all belong to the last part).
-  int32_t krange[kPfMaxTiles];
-  int32_t slot[kPfMaxTiles];
+  int32_t krange[N];
+  int32_t slot[N];
 };
+using PrefillTiles = PrefillTilesT<kPfMaxTiles>;
 
 // floats per (slot, 128-row group) of the split workspace: O transposed [DP][128] (a warp's stores of one column
 // are 128 contiguous bytes), then the rows' running maxima (exp2 domain) and sums
@@ -123,11 +129,11 @@ __device__ __forceinline__ void named_sync(int id) { asm volatile("bar.sync %0, 
 __device__ __forceinline__ void named_sync_n(int id, int n) { asm volatile("bar.sync %0, %1;" :: "r"(id), "r"(n) : "memory"); }
 __device__ __forceinline__ void named_arrive(int id) { asm volatile("bar.arrive %0, 256;" :: "r"(id) : "memory"); }
 
-template <typename T, int DP, bool kPaged = false>
+template <typename T, int DP, bool kPaged = false, int kTiles = kPfMaxTiles>
 __global__ void __launch_bounds__(kPfThreads, 1)
 prefill_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant__ CUtensorMap tmk,
                   const __grid_constant__ CUtensorMap tmv, const __grid_constant__ CUtensorMap tmo,
-                  const __grid_constant__ PrefillTiles tiles,
+                  const __grid_constant__ PrefillTilesT<kTiles> tiles,
                   const PrefillParams p) {
   constexpr int kAtoms = DP / 64;                 // 64-element (128-byte) column groups of a tile
   constexpr uint32_t kAtomBytes = 128 * 128;      // 128 rows x 128 bytes
@@ -556,11 +562,16 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant
         // A row wholly masked in such a tile (never tile 0) keeps its running maximum: all its p are 0.
         if ((kt0 + j + 1) * kPfCols - 1 > min(qi0 + koff, klen - 1)) {
           const int lim = min(qi0 + r + koff, klen - 1) - (kt0 + j) * kPfCols;   // last valid column of this row
+          // the row's valid columns are a prefix: one 32-bit mask per chunk, tested bit by bit (ptxas moves the bits
+          // into predicates seven at a time, R2P, instead of one compare per element)
 #pragma unroll
-          for (int c = 0; c < 4; ++c)
+          for (int c = 0; c < 4; ++c) {
+            const int m = lim - 32 * c;             // last valid column inside this chunk
+            const uint32_t bits = m >= 31 ? 0xffffffffu : (m < 0 ? 0u : (2u << m) - 1u);
 #pragma unroll
             for (int i = 0; i < 32; ++i)
-              if (c * 32 + i > lim) s[c][i] = 0xff800000u;   // -inf
+              if (!((bits >> i) & 1u)) s[c][i] = 0xff800000u;   // -inf
+          }
         }
         // row maximum of the raw logits (scale > 0), four independent chains of 3-input max
         float mx[4];
