@@ -5,6 +5,7 @@ prompt-attention kernel here takes the prompt lengths themselves, so `attn_bias`
 stand-in object that just remembers them (same `from_seqlens` constructor)."""
 from __future__ import annotations
 
+import dataclasses
 from typing import Any, Dict, List, Sequence, Tuple
 
 import torch
@@ -22,40 +23,38 @@ class BlockDiagonalCausalMask:
         return cls(seqlens)
 
 
+@dataclasses.dataclass(repr=False, eq=False)
 class InputMetadata:
+    """The seven constructor fields, in the reference's order (positional and keyword construction both work as
+    there); everything else is derived once after construction.  Derived counts are properties of the tensors'
+    shapes, checked against each other like the reference's asserts (:36-37)."""
+    seq_groups: List[Tuple[List[int], Any]]      # (seq_ids, sampling_params) per group
+    seq_data: Dict[int, Any]                     # seq_id -> SequenceData
+    prompt_lens: List[int]
+    slot_mapping: torch.Tensor                   # [num_valid_tokens] int32
+    context_lens: torch.Tensor                   # [num_generation_tokens] int32
+    max_context_len: int
+    block_tables: torch.Tensor                   # [num_generation_tokens, max_num_blocks_per_seq] int32
 
-    def __init__(
-        self,
-        seq_groups: List[Tuple[List[int], Any]],     # (seq_ids, sampling_params) per group
-        seq_data: Dict[int, Any],                    # seq_id -> SequenceData
-        prompt_lens: List[int],
-        slot_mapping: torch.Tensor,                  # [num_valid_tokens] int32
-        context_lens: torch.Tensor,                  # [num_generation_tokens] int32
-        max_context_len: int,
-        block_tables: torch.Tensor,                  # [num_generation_tokens, max_num_blocks_per_seq] int32
-    ) -> None:
-        self.seq_groups = seq_groups
-        self.seq_data = seq_data
-        self.prompt_lens = prompt_lens
-        self.slot_mapping = slot_mapping
-        self.context_lens = context_lens
-        self.max_context_len = max_context_len
-        self.block_tables = block_tables
+    # derived in __post_init__ (read by the attention layer and the sampler under exactly these names)
+    attn_bias: BlockDiagonalCausalMask = dataclasses.field(init=False)
+    num_prompts: int = dataclasses.field(init=False)
+    num_prompt_tokens: int = dataclasses.field(init=False)
+    num_generation_tokens: int = dataclasses.field(init=False)
+    num_valid_tokens: int = dataclasses.field(init=False)
+    max_num_blocks_per_seq: int = dataclasses.field(init=False)
 
-        self.attn_bias = BlockDiagonalCausalMask.from_seqlens(prompt_lens)
-        self.num_prompts = len(prompt_lens)
-        self.num_prompt_tokens = sum(prompt_lens)
-        self.num_generation_tokens = context_lens.shape[0]
-        self.num_valid_tokens = slot_mapping.shape[0]
-        if block_tables.numel() > 0:
-            self.max_num_blocks_per_seq = block_tables.shape[1]
-        else:
-            self.max_num_blocks_per_seq = 0
-        assert block_tables.shape[0] == self.num_generation_tokens
-        assert context_lens.shape[0] == self.num_generation_tokens
+    def __post_init__(self) -> None:
+        self.attn_bias = BlockDiagonalCausalMask.from_seqlens(self.prompt_lens)
+        self.num_prompts, self.num_prompt_tokens = len(self.prompt_lens), sum(self.prompt_lens)
+        self.num_generation_tokens = int(self.context_lens.shape[0])
+        self.num_valid_tokens = int(self.slot_mapping.shape[0])
+        self.max_num_blocks_per_seq = int(self.block_tables.shape[1]) if self.block_tables.numel() > 0 else 0
+        if self.block_tables.shape[0] != self.num_generation_tokens:
+            raise AssertionError(f"{self.block_tables.shape[0]} block-table rows for {self.num_generation_tokens} "
+                                 "generation tokens")
 
     def __repr__(self) -> str:
-        return (f"InputMetadata(num_valid_tokens={self.num_valid_tokens}, "
-                f"num_prompt_tokens={self.num_prompt_tokens}, num_prompts={self.num_prompts}, "
-                f"prompt_lens={self.prompt_lens}, num_generation_tokens={self.num_generation_tokens}, "
-                f"max_context_len={self.max_context_len}, max_num_blocks_per_seq={self.max_num_blocks_per_seq})")
+        shown = ("num_valid_tokens", "num_prompt_tokens", "num_prompts", "prompt_lens", "num_generation_tokens",
+                 "max_context_len", "max_num_blocks_per_seq")
+        return "InputMetadata(" + ", ".join(f"{k}={getattr(self, k)}" for k in shown) + ")"
