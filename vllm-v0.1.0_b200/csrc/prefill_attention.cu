@@ -180,9 +180,23 @@ static int launch_tc_n(const CUtensorMap& mq, const CUtensorMap& mk, const CUten
   constexpr int smem = 7 * (DP / 64) * 128 * 128 + 1024 + 256;   // Q x 2, K x 2, V x 2, output staging; alignment slack; barriers
   auto kern = prefill_tc_kernel<T, DP, kPaged, kTiles>;
   PA_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-  kern<<<p.tile_major ? dim3(ntiles, p.num_heads) : dim3(p.num_heads, ntiles), kPfThreads, smem, stream>>>(mq, mk, mv, mo, tiles, p);
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = p.tile_major ? dim3(ntiles, p.num_heads) : dim3(p.num_heads, ntiles);
+  cfg.blockDim = dim3(kPfThreads);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  // programmatic dependent launch: barrier set-up, tensor-memory allocation and descriptor prefetch of the CTAs
+  // overlap the tail of the preceding kernel on the stream; the kernel touches no global memory before
+  // griddepcontrol.wait (PA_PREFILL_PDL=0 switches it off)
+  static const bool pdl = [] { const char* e = getenv("PA_PREFILL_PDL"); return !(e && e[0] == '0'); }();
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = pdl ? 1 : 0;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  const cudaError_t e = cudaLaunchKernelEx(&cfg, kern, mq, mk, mv, mo, tiles, p);
   count_launch();
-  return check_cuda(cudaGetLastError(), "prefill_tc_kernel launch");
+  return check_cuda(e, "prefill_tc_kernel launch");
 }
 
 // up to kPfFewTiles entries travel in the small table (see PrefillTilesT)

@@ -246,6 +246,11 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant
   tc05::fence_before_sync();
   __syncthreads();
   tc05::fence_after_sync();
+  // Programmatic dependent launch: everything above touched only parameters and this CTA's own shared / tensor
+  // memory, so it may run while the preceding kernel on the stream is still draining; from here on global memory
+  // is read and written.
+  pdl_launch_dependents();
+  pdl_wait();
   uint32_t tmem;
   asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem) : "r"(tm_slot) : "memory");
 
