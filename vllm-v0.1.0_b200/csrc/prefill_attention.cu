@@ -177,7 +177,7 @@ static int make_page_maps(CUtensorMap* mk, CUtensorMap* mv, const void* key_cach
 template <typename T, int DP, bool kPaged, int kTiles>
 static int launch_tc_n(const CUtensorMap& mq, const CUtensorMap& mk, const CUtensorMap& mv, const CUtensorMap& mo,
                        const PrefillTilesT<kTiles>& tiles, int ntiles, const PrefillParams& p, cudaStream_t stream) {
-  constexpr int smem = 7 * (DP / 64) * 128 * 128 + 1024 + 256;   // Q x 2, K x 2, V x 2, output staging; alignment slack; barriers
+  constexpr int smem = 7 * (DP / 64) * 128 * 128 + 1024 + 288;   // Q x 2, K x 2, V x 2, output staging; alignment slack; barriers
   auto kern = prefill_tc_kernel<T, DP, kPaged, kTiles>;
   PA_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
   cudaLaunchConfig_t cfg = {};

@@ -28,6 +28,30 @@
 
 namespace pa {
 
+#ifdef PA_PF_WATCHDOG
+// debugging aid (compile prefill_attention.cu with -DPA_PF_WATCHDOG and <cstdio>): every mbarrier wait of the prompt
+// kernel that is stuck for ~2^28 clocks says once where it is, and traps later -- the wait-for graph of a deadlock
+__device__ __noinline__ void mbar_wait_dbg(uint32_t bar, uint32_t parity, int line) {
+  const long long t0 = clock64();
+  bool said = false;
+  for (;;) {
+    uint32_t ok;
+    asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                 : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+    if (ok) return;
+    const long long dt = clock64() - t0;
+    if (dt > (1ll << 28) && !said) {
+      said = true;
+      if ((threadIdx.x & 31) == 0 && blockIdx.y == 0 && blockIdx.x < 12)
+        printf("[watchdog] cta (%d,%d) warp %d line %d bar+%u parity %u\n", blockIdx.x, blockIdx.y, threadIdx.x >> 5,
+               line, bar & 1023u, parity);
+    }
+    if (dt > (3ll << 28)) asm volatile("trap;");
+  }
+}
+#define mbar_wait(b, p) mbar_wait_dbg(b, p, __LINE__)
+#endif
+
 constexpr int kPfRows = 256;       // query rows per CTA (two tiles of 128 = TMEM lanes)
 constexpr int kPfCols = 128;       // K/V tokens per tile
 constexpr int kPfMaxTiles = 1024;  // CTAs per launch (the table travels as a kernel parameter)
@@ -164,6 +188,8 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant
   const uint32_t bar_cf = sBar + 160, bar_ce = sBar + 176;   // [2] each: next work item landed / read by everybody
   const uint32_t sClc = sBar + 192;                // [2] x 16 bytes: the scheduler's answers
   const uint32_t bar_vl = sBar + 240;              // kPaged: a V tile whose tail is zeroed lands here first
+  const uint32_t bar_sf = sBar + 248;              // [2]: group i has filled the staging buffer with a whole output tile
+  const uint32_t bar_sd = sBar + 264;              // [2]: ... and the store warp has sent it off and released the buffer
   const uint32_t tm_slot = sBar + 120;
   const uint32_t sc_slot = sBar + 124;             // scale_log2, re-read after the ping-pong barrier (see below)
 
@@ -197,7 +223,7 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant
   // Item n + 1 of this CTA is the answer to the n-th request (slot n & 1), issued by the scheduler thread when
   // it starts item n.  Every thread that works on items calls next_item() once per item, in order: it waits for
   // the answer, reads it, releases the slot, and learns whether to go on.
-  constexpr uint32_t kClcReaders = 256 + 1 + 1;    // softmax threads, issuer lane, producer lane
+  constexpr uint32_t kClcReaders = 256 + 1 + 1 + 1;   // softmax threads, issuer lane, producer lane, store lane
   auto request_next = [&](int n) {                // scheduler thread only
     const uint32_t slot = n & 1;
     mbar_wait(bar_ce + 8 * slot, ((n >> 1) & 1) ^ 1);   // first use of a slot passes immediately
@@ -238,6 +264,7 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant
       mbar_init(bar_s + 8 * s, 1); mbar_init(bar_p + 8 * s, 128); mbar_init(bar_o + 8 * s, 1);
       mbar_init(bar_ph + 8 * s, 128);
       mbar_init(bar_cf + 8 * s, 1); mbar_init(bar_ce + 8 * s, kClcReaders);
+      mbar_init(bar_sf + 8 * s, 128); mbar_init(bar_sd + 8 * s, 1);
     }
     asm volatile("st.shared.f32 [%0], %1;" :: "r"(sc_slot), "f"(p.scale_log2) : "memory");
     mbar_init_fence();
@@ -517,6 +544,37 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant
     }
     // the last commits must have landed in this CTA's shared memory before the CTA may exit
     mbar_wait(bar_ve + 8 * ((g0 - 1) & 1), ((g0 - 1) >> 1) & 1);
+  } else if (warp == 10) {
+    // ===================== output store =====================
+    // A whole 128-row output tile leaves as TMA stores from the staging buffer.  The softmax group only fills the
+    // buffer (tensor memory -> registers -> swizzled shared memory), fences and arrives; this warp issues the
+    // stores, waits until they have read the buffer and hands it on -- 1000 clk per tile that used to sit in the
+    // group's own chain (the storing thread waited for the TMA read, and its warp with it).  Partial tiles and the
+    // parts of split entries are written by the groups themselves, which then release the buffer.
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 56;");
+    int cf[2] = {0, 0};                             // whole tiles handed over by group A / B so far (phase of bar_sf)
+    for (int n = 0;; ++n) {
+#pragma unroll
+      for (int g = 0; g < 2; ++g) {
+        const int ni = g ? it.nB : it.nA;
+        const int qi0 = it.q0 + 128 * g;
+        if (ni > 0 && it.slot < 0 && it.qlen - qi0 >= 128) {
+          mbar_wait(bar_sf + 8 * g, cf[g] & 1);
+          ++cf[g];
+          if (lane == 0) {
+#pragma unroll
+            for (int a = 0; a < kAtoms; ++a)
+              if (a * 64 < p.head_size) tc05::tma_store_3d(&tmo, sStg + a * kAtomBytes, a * 64, it.head, it.qtok0 + qi0);
+            tc05::tma_store_commit();
+            tc05::tma_store_wait_read();
+            mbar_arrive(bar_stg);
+            mbar_arrive(bar_sd + 8 * g);
+          }
+          __syncwarp();
+        }
+      }
+      if (!next_item(n, it, lane == 0)) break;
+    }
   } else if (warp >= 10) {
     // register donors.  384 threads x 168 registers is the CTA's pool = 128 x 56 + 256 x 224; setmaxnreg must be
     // the same instruction in all four warps of a warpgroup (warps 8-11), whatever branch they sit in
@@ -530,6 +588,7 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant
     const uint32_t tS = lane_base + kTmS + 128 * grp, tO = lane_base + kTmO + 128 * grp;
     const int bar_mine = 1 + grp, bar_other = 2 - grp;
     int cs = 0, co = 0;                             // S tiles / finished tiles of this group so far (barrier phases)
+    int ch = 0, chw = 0;                            // tiles handed to the store warp / of those, seen off (phase of bar_sd)
     for (int n = 0;; ++n) {
       const int nA = it.nA, nB = it.nB;
       const int ni = grp ? nB : nA;
@@ -658,6 +717,12 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant
       // partial tile (rows past the prompt belong to the next one) leaves as row-contiguous 16-byte stores of
       // its valid rows instead.  The staging buffer is used in turns, A and B of item 0, A and B of item 1, ...
       // (use u = 2 n + group waits for the u-th release); a group without a tile only passes the turn on.
+      bool handed = false;                            // this item's tile went to the store warp, which releases the buffer
+      // The turn barrier tells phases apart by parity only.  A release that the store warp makes on this group's
+      // behalf comes whenever the TMA read is over -- possibly after this group has run through a short next item --
+      // and a wait that starts before it would take the phase before for the one it wants.  So a handed tile is
+      // first seen off (its own barrier, one phase per handed tile, consumed in order), then the turn is awaited.
+      if (r == 0 && ch > chw) { mbar_wait(bar_sd + 8 * grp, chw & 1); ++chw; }
       if (r == 0) mbar_wait(bar_stg, (grp & 1) ^ 1);   // u & 1 == group
       if (ni > 0) {
         mbar_wait(bar_o + 8 * grp, co & 1);
@@ -705,15 +770,10 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant
         }
         const int valid = min(128, qlen - qi0);       // rows of this tile inside the prompt
         if (valid == 128) {
-          tc05::fence_async_smem();
-          named_sync_n(3 + grp, 128);
-          if (r == 0) {
-#pragma unroll
-            for (int a = 0; a < kAtoms; ++a)
-              if (a * 64 < D) tc05::tma_store_3d(&tmo, sStg + a * kAtomBytes, a * 64, head, qtok0 + qi0);
-            tc05::tma_store_commit();
-            tc05::tma_store_wait_read();
-          }
+          tc05::fence_async_smem();                   // my stores -> visible to the TMA unit
+          mbar_arrive(bar_sf + 8 * grp);              // the store warp takes it from here and releases the buffer
+          handed = true;
+          ++ch;
         } else {
           named_sync_n(3 + grp, 128);
           const int cpr = D / 8;                      // 16-byte chunks per row: 8, 10, 12 or 16
@@ -730,8 +790,8 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant
         }
         }
       }
-      if (r == 0) mbar_arrive(bar_stg);
-      if (ni > 0) stamp(p.dbg, tl, 3, cs - 1, grp);     // output written (row 3 of the stamp table)
+      if (r == 0 && !handed) mbar_arrive(bar_stg);
+      if (ni > 0) stamp(p.dbg, tl, 3, cs - 1, grp);     // output written or handed to the store warp (row 3 of the stamp table)
       if (!next_item(n, it, true)) break;
     }
   }
