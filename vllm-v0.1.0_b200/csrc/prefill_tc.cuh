@@ -1,10 +1,12 @@
 // tcgen05 prompt-attention kernel (16-bit types).  See prefill_attention.cu for the operator.
 //
 // One CTA = 256 query rows of one (prompt, head), as two 128-row tiles A and B that share every K/V
-// tile.  Twelve warps (two of them only donate their registers), three roles:
+// tile.  Twelve warps, four roles (warp 11 only donates its registers):
 //   warps 0-3 / 4-7  softmax group of tile A / B: thread r owns row r (TMEM lane r % 128)
-//   warp 8           TMA producer: Q tiles once, then K_j / V_j through two-stage rings
+//   warp 8           TMA producer: Q tiles once, then K_j / V_j through two-stage rings (packed rows, or the
+//                    pages of the paged cache as they lie)
 //   warp 9           MMA issuer: one thread issues every tcgen05.mma of the CTA
+//   warp 10          output store: TMA stores of finished 128-row tiles from the staging buffer
 // Tensor memory (512 columns): S_A | S_B | O_A | O_B, 128 fp32 columns each; the probabilities
 // P_i overwrite the first 64 columns of S_i (two 16-bit values per column) and are consumed
 // from there as the A operand of P.V.  Per tile the dependency chain is
@@ -55,7 +57,7 @@ __device__ __noinline__ void mbar_wait_dbg(uint32_t bar, uint32_t parity, int li
 constexpr int kPfRows = 256;       // query rows per CTA (two tiles of 128 = TMEM lanes)
 constexpr int kPfCols = 128;       // K/V tokens per tile
 constexpr int kPfMaxTiles = 1024;  // CTAs per launch (the table travels as a kernel parameter)
-constexpr int kPfThreads = 384;   // 8 softmax warps + producer + issuer + 2 idle warps that only donate registers
+constexpr int kPfThreads = 384;   // 8 softmax warps + producer + issuer + output store + 1 warp that only donates registers
 
 // A sequence has qlen query rows (packed from token qtok0 of q / out) and klen >= qlen keys (packed from
 // token ktok0 of k / v).  Query row i sees keys 0 .. i + (klen - qlen): plain prompt attention is
