@@ -192,6 +192,7 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant
   const uint32_t bar_vl = sBar + 240;              // kPaged: a V tile whose tail is zeroed lands here first
   const uint32_t bar_sf = sBar + 248;              // [2]: group i has filled the staging buffer with a whole output tile
   const uint32_t bar_sd = sBar + 264;              // [2]: ... and the store warp has sent it off and released the buffer
+  const uint32_t bar_bl = sBar + 280;              // group B has taken its last turn of the item (see the ping-pong below)
   const uint32_t tm_slot = sBar + 120;
   const uint32_t sc_slot = sBar + 124;             // scale_log2, re-read after the ping-pong barrier (see below)
 
@@ -260,6 +261,7 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant
     mbar_init(bar_qe, 1); mbar_init(bar_qe1, 1);
     mbar_init(bar_stg, 1);
     mbar_init(bar_vl, 1);
+    mbar_init(bar_bl, 1);
     for (int s = 0; s < 2; ++s) {
       mbar_init(bar_kf + 8 * s, 1); mbar_init(bar_ke + 8 * s, 1);
       mbar_init(bar_vf + 8 * s, 1); mbar_init(bar_ve + 8 * s, 1);
@@ -608,6 +610,7 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant
       // A's first tile of an item takes no turn (it may share the unit with the tail of B's previous item; waiting
       // for B to get there cost 2000 clk per item), from then on the two alternate.
       const bool pingpong = nB > 0;
+      if (!pingpong && grp == 1 && r == 0) mbar_arrive(bar_bl);   // nothing of A's to consume in this item (see below)
       for (int j = 0; j < ni; ++j) {
         stamp(p.dbg, tl, grp, cs + j, 0);
         mbar_wait(bar_s + 8 * grp, (cs + j) & 1);
@@ -673,6 +676,12 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant
         float sum[4] = {0.f, 0.f, 0.f, 0.f};
         stamp(p.dbg, tl, grp, cs + j, 2);
         if (pingpong && j < nA && (grp == 1 || j > 0)) named_sync(bar_mine);   // B's extra (diagonal) tile runs after A's last: no turn to wait for
+        // B has now consumed every arrival A made in this item.  A's first arrival of the NEXT item must not come
+        // before that (two arrivals with no sync between them would complete the named barrier with nobody
+        // waiting): B says so here, once per item, A checks in its epilogue before it leaves the item.  It used to be
+        // a margin of a few thousand clocks -- A's epilogue and first tile against B's lag of half a period -- not a
+        // guarantee.
+        if (pingpong && grp == 1 && j == nA - 1 && r == 0) mbar_arrive(bar_bl);
         // ptxas moves arithmetic (and MUFU) across BAR.SYNC freely; what it cannot move is a value loaded
         // after the barrier, so the section's multiplier is re-read from shared memory here
         float sc;
@@ -730,6 +739,7 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant
         mbar_wait(bar_o + 8 * grp, co & 1);
         ++co;
         tc05::fence_after_sync();
+        if (grp == 0) mbar_wait(bar_bl, n & 1);       // B has taken its last turn of this item (one phase per item)
         stamp(p.dbg, tl, grp, cs - 1, 6);             // O ready (the item's last P.V has run)
         if (slot >= 0) {
           // one part of a split context: O as it stands (relative to m_run, not normalised), m_run and l_run go to
