@@ -9,6 +9,7 @@
 #include <cstring>
 #include <map>
 #include <mutex>
+#include <vector>
 #include <utility>
 
 #include "decode_attention.cuh"
@@ -50,9 +51,13 @@ struct Workspace {
   size_t bytes = 0;
   size_t ticket_bytes = 0;
   bool dirty = false;
+  bool in_graph = false;   // handed out while the stream was being captured: a CUDA graph holds the pointer
 };
 static std::mutex g_ws_mu;
 static std::map<std::pair<int, cudaStream_t>, Workspace> g_ws;
+// buffers that a captured graph may still replay into; kept until pa_release_workspaces instead of being freed when a
+// later, larger call outgrows them
+static std::vector<std::pair<int, void*>> g_ws_retired;
 
 static int get_workspace(cudaStream_t stream, size_t ticket_bytes, size_t part_bytes, uint32_t** tickets,
                          float** parts) {
@@ -71,7 +76,8 @@ static int get_workspace(cudaStream_t stream, size_t ticket_bytes, size_t part_b
                        "pa_decode_attention_reserve for this shape before capturing", ticket_bytes + part_bytes);
     if (w.ptr) {
       PA_CUDA_TRY(cudaStreamSynchronize(stream));
-      PA_CUDA_TRY(cudaFree(w.ptr));
+      if (w.in_graph) g_ws_retired.emplace_back(dev, w.ptr);
+      else PA_CUDA_TRY(cudaFree(w.ptr));
       w = Workspace();
     }
     const size_t tb = ticket_bytes * 2;            // head-room: item count may grow
@@ -84,6 +90,10 @@ static int get_workspace(cudaStream_t stream, size_t ticket_bytes, size_t part_b
   if (w.dirty) {
     PA_CUDA_TRY(cudaMemsetAsync(w.ptr, 0, w.ticket_bytes, stream));
     w.dirty = false;
+  }
+  if (!w.in_graph) {
+    cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+    if (cudaStreamIsCapturing(stream, &cap) == cudaSuccess && cap != cudaStreamCaptureStatusNone) w.in_graph = true;
   }
   *tickets = static_cast<uint32_t*>(w.ptr);
   *parts = reinterpret_cast<float*>(static_cast<char*>(w.ptr) + w.ticket_bytes);
@@ -319,6 +329,14 @@ int pa_release_workspaces(void) {
     if (it->first.first == dev) {
       if (it->second.ptr) cudaFree(it->second.ptr);
       it = pa::g_ws.erase(it);
+    } else {
+      ++it;
+    }
+  }
+  for (auto it = pa::g_ws_retired.begin(); it != pa::g_ws_retired.end();) {
+    if (it->first == dev) {
+      cudaFree(it->second);
+      it = pa::g_ws_retired.erase(it);
     } else {
       ++it;
     }

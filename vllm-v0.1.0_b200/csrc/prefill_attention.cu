@@ -265,32 +265,44 @@ prefill_merge_kernel(const __grid_constant__ MergeTable t, const float* __restri
 
 // scratch for the parts, per (device, stream) like the decode kernel's; a request that would have to grow while
 // the stream is being captured is refused (the caller then simply does not split)
-struct SplitScratch { void* ptr = nullptr; size_t bytes = 0; };
+struct SplitScratch { void* ptr = nullptr; size_t bytes = 0; bool in_graph = false; };
 static std::mutex g_split_mu;
 static std::map<std::pair<int, cudaStream_t>, SplitScratch> g_split_ws;
+static std::vector<std::pair<int, void*>> g_split_retired;   // outgrown buffers a captured graph may still replay into
 
 static float* split_scratch(cudaStream_t stream, size_t bytes) {
   int dev = 0;
   if (cudaGetDevice(&dev) != cudaSuccess) return nullptr;
   std::lock_guard<std::mutex> lock(g_split_mu);
   SplitScratch& w = g_split_ws[std::make_pair(dev, stream)];
+  cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+  if (cudaStreamIsCapturing(stream, &cap) != cudaSuccess) return nullptr;
   if (w.bytes < bytes) {
-    cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
-    if (cudaStreamIsCapturing(stream, &cap) != cudaSuccess || cap != cudaStreamCaptureStatusNone) return nullptr;
+    if (cap != cudaStreamCaptureStatusNone) return nullptr;
     if (w.ptr) {
       if (cudaStreamSynchronize(stream) != cudaSuccess) return nullptr;
-      cudaFree(w.ptr);
+      if (w.in_graph) g_split_retired.emplace_back(dev, w.ptr);
+      else cudaFree(w.ptr);
       w = SplitScratch();
     }
     const size_t want = std::max<size_t>(bytes, size_t{16} << 20);
     if (cudaMalloc(&w.ptr, want) != cudaSuccess) { cudaGetLastError(); w = SplitScratch(); return nullptr; }
     w.bytes = want;
   }
+  if (cap != cudaStreamCaptureStatusNone) w.in_graph = true;   // a graph will hold this pointer
   return static_cast<float*>(w.ptr);
 }
 
 void release_prefill_scratch(int dev) {             // pa_release_workspaces
   std::lock_guard<std::mutex> lock(g_split_mu);
+  for (auto it = g_split_retired.begin(); it != g_split_retired.end();) {
+    if (it->first == dev) {
+      cudaFree(it->second);
+      it = g_split_retired.erase(it);
+    } else {
+      ++it;
+    }
+  }
   for (auto it = g_split_ws.begin(); it != g_split_ws.end();) {
     if (it->first.first == dev) {
       if (it->second.ptr) cudaFree(it->second.ptr);
