@@ -184,6 +184,59 @@ PA_API int pa_decode_attention_plan(int32_t num_seqs, int32_t num_heads,
                              int32_t max_context_len, int32_t dtype,
                              pa_decode_tuning* plan_out);
 
+/*
+ * No counterpart in the reference: this entry point exists for hosts that are
+ * not allowed to allocate device memory.
+ *
+ * pa_decode_attention keeps the partial results of a context that is split
+ * over several CTAs in a buffer it cudaMalloc's on first use and grows later.
+ * Some callers cannot live with that: an engine that hands the whole GPU to
+ * its own pool at start-up and leaves nothing for a driver allocation to
+ * succeed from, a plug-in running under a host whose rules forbid cudaMalloc
+ * after initialisation, a latency-critical loop that cannot take the implicit
+ * device synchronisation an allocation or a free may bring.  For them this
+ * variant computes the same operator (same arguments and results as
+ * pa_decode_attention_ex) but keeps those partial results in a fixed array
+ * compiled into the library.  It never calls cudaMalloc, cudaFree or any
+ * routine that allocates; apart from the kernel launch it issues one
+ * cudaMemsetAsync on `stream`.
+ *
+ * Limits.  The array is PA_STATIC_SCRATCH_BYTES long and every GPU that loads
+ * the library holds one copy of it until the process exits.  When the launch
+ * shape splits the context (num_splits > 1 in the plan) the call needs
+ *   num_seqs * num_heads                                  <= PA_STATIC_SCRATCH_MAX_ITEMS
+ *   num_seqs * num_heads * num_splits * (head_size+2) * 4 <= PA_STATIC_SCRATCH_BYTES
+ *                                                            - 4 * PA_STATIC_SCRATCH_MAX_ITEMS
+ * and returns PA_ERR_INVALID_ARGUMENT, with the sizes in pa_last_error(), when
+ * it does not fit; nothing is launched then.  Automatic plans stay below
+ * 148 * 32 (item, split) pairs and always fit; a forced num_splits may not --
+ * lower it or use pa_decode_attention.  Shapes that do not split use no scratch
+ * and have no limit.
+ *
+ * Sharing.  There is ONE array per device, whatever the stream.  The call
+ * clears the part that has to start from zero, so whatever an earlier call
+ * left behind does no harm, but two calls that can be on the GPU at the same
+ * time (different streams, or one stream from two host threads without
+ * ordering) overwrite each other's partial results: keep calls to this entry
+ * point ordered one after the other on each device.  pa_decode_attention and
+ * the other entry points use their own buffers and may overlap with it.
+ *
+ * First call.  The first call on each device looks up the array's device
+ * address (with that device current) and remembers it.  Make that first call
+ * ahead of any CUDA stream capture on the device.
+ */
+#define PA_STATIC_SCRATCH_BYTES (4 * 1024 * 1024)
+#define PA_STATIC_SCRATCH_MAX_ITEMS 16384
+PA_API int pa_decode_attention_static(void* out, const void* query, const void* key_cache,
+                               const void* value_cache, float scale,
+                               const int32_t* block_tables,
+                               const int32_t* context_lens, int32_t num_seqs,
+                               int32_t num_heads, int32_t head_size,
+                               int32_t block_size, int32_t max_num_blocks_per_seq,
+                               int32_t max_context_len, int64_t q_stride,
+                               int32_t dtype, const pa_decode_tuning* tuning,
+                               void* stream);
+
 /* ------------------------------------------------------------------------ */
 /* prompt (prefill) attention                                               */
 /* ------------------------------------------------------------------------ */

@@ -65,6 +65,8 @@ SIGNATURES = {
                                       _i64, _i32, _vp]),
     "pa_decode_attention_ex": (C.c_int, [_vp, _vp, _vp, _vp, _f32, _vp, _vp, _i32, _i32, _i32, _i32, _i32, _i32,
                                          _i64, _i32, C.POINTER(DecodeTuning), _vp]),
+    "pa_decode_attention_static": (C.c_int, [_vp, _vp, _vp, _vp, _f32, _vp, _vp, _i32, _i32, _i32, _i32, _i32, _i32,
+                                             _i64, _i32, C.POINTER(DecodeTuning), _vp]),
     "pa_decode_attention_reserve": (C.c_int, [_i32, _i32, _i32, _i32, _i32, _i32, _i32, C.POINTER(DecodeTuning), _vp]),
     "pa_decode_attention_plan": (C.c_int, [_i32, _i32, _i32, _i32, _i32, _i32, C.POINTER(DecodeTuning)]),
     "pa_prefill_attention": (C.c_int, [_vp, _vp, _vp, _vp, C.POINTER(_i32), _i32, _i32, _i32, _i64, _i64, _i64, _i64,

@@ -308,6 +308,112 @@ static int decode(void* out, const void* query, const void* key_cache, const voi
   return rc;
 }
 
+
+// ---------------------------------------------------------------------------
+// decode attention for callers that must not allocate (pa_decode_attention_static)
+//
+// The split-context partials and tickets live in an array that is part of the library image instead of
+// a cudaMalloc'ed buffer: [0, kStaticTicketBytes) tickets, the rest partial results.  Every device that
+// loads the library carries its own copy until the process exits.
+// ---------------------------------------------------------------------------
+constexpr size_t kStaticScratchBytes = PA_STATIC_SCRATCH_BYTES;
+constexpr size_t kStaticTicketBytes = PA_STATIC_SCRATCH_MAX_ITEMS * sizeof(uint32_t);
+static_assert(kStaticTicketBytes % 256 == 0 && kStaticTicketBytes < kStaticScratchBytes, "ticket region");
+static __device__ __align__(256) unsigned char g_static_scratch[kStaticScratchBytes];
+
+// Device address of g_static_scratch on the current device.  In host code the array's name is only a handle
+// for the runtime -- it is not an address a kernel can use -- so the address is asked for once per device,
+// with that device current, and remembered.
+static int static_scratch_address(unsigned char** base) {
+  static std::mutex mu;
+  static unsigned char* cached[64] = {nullptr};
+  int dev = 0;
+  PA_CUDA_TRY(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64) return set_error(PA_ERR_INVALID_ARGUMENT, "device ordinal %d out of range (max 63)", dev);
+  std::lock_guard<std::mutex> lock(mu);
+  if (!cached[dev]) {
+    void* ptr = nullptr;
+    PA_CUDA_TRY(cudaGetSymbolAddress(&ptr, g_static_scratch));
+    if (!ptr || (reinterpret_cast<uintptr_t>(ptr) & 255u))
+      return set_error(PA_ERR_CUDA, "cudaGetSymbolAddress returned an unusable address for the static scratch");
+    cached[dev] = static_cast<unsigned char*>(ptr);
+  }
+  *base = cached[dev];
+  return PA_OK;
+}
+
+static int decode_static(void* out, const void* query, const void* key_cache, const void* value_cache, float scale,
+                         const int32_t* block_tables, const int32_t* context_lens, int32_t num_seqs,
+                         int32_t num_heads, int32_t head_size, int32_t block_size, int32_t max_num_blocks_per_seq,
+                         int32_t max_context_len, int64_t q_stride, int32_t dtype, const pa_decode_tuning* tuning,
+                         cudaStream_t stream) {
+  int rc = check_shape(head_size, block_size, dtype);
+  if (rc != PA_OK) return rc;
+  if (num_seqs < 0 || num_heads <= 0 || max_num_blocks_per_seq < 0 || max_context_len < 0)
+    return set_error(PA_ERR_INVALID_ARGUMENT, "bad sizes (seqs %d, heads %d, max blocks %d, max context %d)",
+                     num_seqs, num_heads, max_num_blocks_per_seq, max_context_len);
+  if (num_seqs == 0) return PA_OK;
+  if (num_seqs > 65535) return set_error(PA_ERR_INVALID_ARGUMENT, "too many sequences: %d (max 65535)", num_seqs);
+  if (!out || !query || !key_cache || !value_cache || !block_tables || !context_lens)
+    return set_error(PA_ERR_INVALID_ARGUMENT, "null pointer");
+  if ((reinterpret_cast<uintptr_t>(key_cache) | reinterpret_cast<uintptr_t>(value_cache)) & 15u)
+    return set_error(PA_ERR_INVALID_ARGUMENT, "key/value cache must be 16-byte aligned");
+  const int es = dtype_size(dtype);
+  if (reinterpret_cast<uintptr_t>(query) % es || reinterpret_cast<uintptr_t>(out) % es)
+    return set_error(PA_ERR_INVALID_ARGUMENT, "query/out are not element-aligned");
+
+  pa_decode_tuning t = {0, 0, 0, 0};
+  if (tuning) t = *tuning;
+  if (t.variant < 0 || t.variant > 3) return set_error(PA_ERR_INVALID_ARGUMENT, "invalid variant %d", t.variant);
+  int pps = 0;
+  rc = make_plan(num_seqs, num_heads, head_size, block_size, max_context_len, dtype, &t, &pps);
+  if (rc != PA_OK) return rc;
+
+  DecodeLaunch l;
+  std::memset(&l, 0, sizeof(l));
+  DecodeParams& p = l.params;
+  p.out = out; p.q = query; p.k_cache = key_cache; p.v_cache = value_cache;
+  p.block_tables = block_tables; p.context_lens = context_lens;
+  p.q_stride = q_stride;
+  p.scale_log2 = scale * 1.4426950408889634f;
+  p.num_heads = num_heads;
+  p.max_blocks_per_seq = max_num_blocks_per_seq;
+  p.pages_per_split = pps;
+  p.num_splits = t.num_splits;
+  p.num_stages = t.num_stages;
+  p.q_vec_ok = (reinterpret_cast<uintptr_t>(query) % 16 == 0) && ((q_stride * es) % 16 == 0);
+  p.num_seqs = num_seqs;
+  p.group_rows = group_rows_for(t.variant >= 2, t.variant, t.num_warps, num_seqs, dtype, block_size,
+                                decode_smem_bytes(dtype, head_size, block_size, pps, t.num_warps, t.num_stages, t.variant >= 2));
+  if (t.num_splits > 1) {
+    const size_t items = static_cast<size_t>(num_seqs) * num_heads;
+    const size_t ticket_bytes = items * sizeof(uint32_t);
+    const size_t part_bytes = items * t.num_splits * (head_size + 2) * sizeof(float);
+    if (ticket_bytes > kStaticTicketBytes || part_bytes > kStaticScratchBytes - kStaticTicketBytes)
+      return set_error(PA_ERR_INVALID_ARGUMENT,
+                       "pa_decode_attention_static: %zu (sequence, head) items in %d context splits need %zu B of tickets and "
+                       "%zu B of partial results; the built-in scratch holds %zu B and %zu B (PA_STATIC_SCRATCH_MAX_ITEMS "
+                       "items, PA_STATIC_SCRATCH_BYTES in all).  Pass a tuning with fewer num_splits, or use "
+                       "pa_decode_attention", items, t.num_splits, ticket_bytes, part_bytes, kStaticTicketBytes,
+                       kStaticScratchBytes - kStaticTicketBytes);
+    unsigned char* base = nullptr;
+    rc = static_scratch_address(&base);
+    if (rc != PA_OK) return rc;
+    // the array keeps whatever the previous call (or a failed launch) left in it; tickets must count from zero
+    PA_CUDA_TRY(cudaMemsetAsync(base, 0, (ticket_bytes + 255) / 256 * 256, stream));
+    p.ws_ticket = reinterpret_cast<uint32_t*>(base);
+    p.ws_part = reinterpret_cast<float*>(base + kStaticTicketBytes);
+  }
+  l.num_seqs = num_seqs; l.head_size = head_size; l.block_size = block_size;
+  l.num_warps = t.num_warps; l.staged = (t.variant >= 2); l.stream = stream;
+  l.pdl = false;   // the launch follows a memset node, not a kernel: nothing to overlap with
+  switch (dtype) {
+    case PA_F16:  return launch_decode_f16(l);
+    case PA_BF16: return launch_decode_bf16(l);
+    default:      return launch_decode_f32(l);
+  }
+}
+
 }  // namespace pa
 
 namespace pa { void release_prefill_scratch(int dev); }   // prefill_attention.cu
@@ -370,6 +476,16 @@ int pa_decode_attention_reserve(int32_t num_seqs, int32_t num_heads, int32_t hea
   return pa::decode(nullptr, nullptr, nullptr, nullptr, 1.f, nullptr, nullptr, num_seqs, num_heads, head_size,
                     block_size, max_num_blocks_per_seq, max_context_len, head_size, dtype, tuning,
                     static_cast<cudaStream_t>(stream), true);
+}
+
+int pa_decode_attention_static(void* out, const void* query, const void* key_cache, const void* value_cache,
+                               float scale, const int32_t* block_tables, const int32_t* context_lens,
+                               int32_t num_seqs, int32_t num_heads, int32_t head_size, int32_t block_size,
+                               int32_t max_num_blocks_per_seq, int32_t max_context_len, int64_t q_stride,
+                               int32_t dtype, const pa_decode_tuning* tuning, void* stream) {
+  return pa::decode_static(out, query, key_cache, value_cache, scale, block_tables, context_lens, num_seqs,
+                           num_heads, head_size, block_size, max_num_blocks_per_seq, max_context_len, q_stride,
+                           dtype, tuning, static_cast<cudaStream_t>(stream));
 }
 
 int pa_decode_attention_plan(int32_t num_seqs, int32_t num_heads, int32_t head_size, int32_t block_size,
