@@ -35,7 +35,9 @@
 extern "C" {
 #endif
 
-#define PA_ABI_VERSION 1
+/* 2: pa_decode_attention_reserve, pa_decode_attention_static, pa_reshape_and_cache_ex; the prompt kernels keep
+ * library-owned scratch.  Bindings compare pa_abi_version() with the value they were built against. */
+#define PA_ABI_VERSION 2
 
 #if defined(__GNUC__) || defined(__clang__)
 #define PA_API __attribute__((visibility("default")))
@@ -346,6 +348,27 @@ PA_API int pa_reshape_and_cache(const void* key, const void* value, void* key_ca
                          int32_t head_size, int32_t block_size,
                          int64_t key_stride, int64_t value_stride,
                          int32_t dtype, void* stream);
+
+/* What the caller knows about slot_mapping (it lives on the device, the library cannot look): a performance hint
+ * only, the result is the same whatever is passed. */
+enum pa_slot_pattern {
+  PA_SLOTS_AUTO = 0,      /* nothing known */
+  PA_SLOTS_SCATTERED = 1, /* every token in a block of its own: a decode step (worker.py:170-199)    */
+  PA_SLOTS_RUNS = 2       /* consecutive slots: prompt tokens (worker.py:138-167), or a mixed batch  */
+};
+
+/* pa_reshape_and_cache with that hint.  A decode step of ~100..512 sequences is served by a
+ * one-CTA-per-token element sweep when the caller declares PA_SLOTS_SCATTERED (about 15 % faster than the tile
+ * mover there); everything else, and every call without a hint, goes through the tile mover, which merges
+ * the tokens of a block into whole sectors.
+ * replaces: the same operator, cache_ops.reshape_and_cache (csrc/cache.cpp:17-22); the hint stands for what the
+ *           call site knows from InputMetadata.num_prompt_tokens (vllm/model_executor/layers/attention.py:129-140). */
+PA_API int pa_reshape_and_cache_ex(const void* key, const void* value, void* key_cache,
+                            void* value_cache, const int32_t* slot_mapping,
+                            int32_t num_tokens, int32_t num_heads,
+                            int32_t head_size, int32_t block_size,
+                            int64_t key_stride, int64_t value_stride,
+                            int32_t dtype, int32_t slot_pattern, void* stream);
 
 /*
  * replaces: cache_ops.gather_cached_kv

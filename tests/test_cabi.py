@@ -36,7 +36,8 @@ def test_header_symbols_are_exported_and_bound():
 
 def test_version_and_target():
     lib = _cabi.lib()
-    assert lib.pa_abi_version() == 1
+    declared = int(re.search(r"#define PA_ABI_VERSION (\d+)", open(HEADER).read()).group(1))
+    assert lib.pa_abi_version() == declared == _cabi.PA_ABI_VERSION
     assert lib.pa_compiled_sm() == 100
     assert lib.pa_launch_count() == 0 or lib.pa_launch_count() > 0
 
@@ -160,6 +161,14 @@ def test_missing_library_fails_loudly(monkeypatch, tmp_path):
     monkeypatch.setattr(_cabi, "_lib", None)
     monkeypatch.setattr(_cabi, "LIB_PATH", str(tmp_path / "libpaged_b200.so"))
     with pytest.raises(RuntimeError, match="no CPU or PyTorch fallback"):
+        _cabi.lib()
+
+
+def test_stale_library_is_refused(monkeypatch):
+    """A library built from an older header must not be bound silently (symbols may be missing or changed)."""
+    monkeypatch.setattr(_cabi, "_lib", None)
+    monkeypatch.setattr(_cabi, "PA_ABI_VERSION", _cabi.PA_ABI_VERSION + 1)
+    with pytest.raises(RuntimeError, match="C ABI version"):
         _cabi.lib()
 
 

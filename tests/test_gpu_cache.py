@@ -83,6 +83,33 @@ def test_reshape_and_gather(dtype, tokens, heads, head_size, block_size):
     dk2, dv2 = kc.to(DEV), vc.to(DEV)
     cache_ops.reshape_and_cache(k2, v2, dk2, dv2, ds)
     assert torch.equal(dk2, dk) and torch.equal(dv2, dv)
+    # the slot-pattern hint picks a kernel (97..512 "scattered" tokens: the per-token element sweep), never the result
+    for hint in ("scattered", "runs"):
+        dk3, dv3 = kc.to(DEV), vc.to(DEV)
+        cache_ops.reshape_and_cache(dq[:, 1], dq[:, 2], dk3, dv3, ds, slots=hint)
+        assert torch.equal(dk3, dk) and torch.equal(dv3, dv), hint
+
+
+@pytest.mark.parametrize("tokens", [128, 512])
+def test_reshape_hint_is_only_a_hint(tokens):
+    """Consecutive slots declared "scattered" and scattered slots declared "runs": the wrong hint costs time, not bits."""
+    from vllm_b200 import cache_ops
+    h, d, b, dtype = 8, 128, 16, torch.float16
+    g = torch.Generator().manual_seed(tokens)
+    nb = tokens // b + 5
+    qkv = torch.randn((tokens, 3, h, d), generator=g).to(dtype)
+    for slots, hint in ((torch.arange(7, 7 + tokens, dtype=torch.int32), "scattered"),
+                        ((torch.randperm(nb, generator=g)[:tokens // b + 1].repeat_interleave(b)[:tokens] * b
+                          + torch.arange(tokens) % b).to(torch.int32), "scattered"),
+                        (torch.randperm(nb * b, generator=g)[:tokens].to(torch.int32), "runs")):
+        wk, wv = torch.zeros(nb, h, d // 8, b, 8, dtype=dtype), torch.zeros(nb, h, d, b, dtype=dtype)
+        c_oracle.reshape_and_cache(qkv[:, 1], qkv[:, 2], wk, wv, slots)
+        dk, dv = torch.zeros_like(wk, device=DEV), torch.zeros_like(wv, device=DEV)
+        dq = qkv.to(DEV)
+        cache_ops.reshape_and_cache(dq[:, 1], dq[:, 2], dk, dv, slots.to(DEV), slots=hint)
+        assert _same_bits(dk, wk) and _same_bits(dv, wv)
+    with pytest.raises(RuntimeError):
+        cache_ops.reshape_and_cache(dq[:, 1], dq[:, 2], dk, dv, slots.to(DEV), slots="sorted")
 
 
 def test_reshape_with_unaligned_rows():

@@ -12,8 +12,10 @@ import threading
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "lib", "libpaged_b200.so")
 
+PA_ABI_VERSION = 2          # include/paged_attention_b200.h; lib() refuses a library that reports another
 PA_F16, PA_BF16, PA_F32 = 0, 1, 2
 PA_COPY_D2D, PA_COPY_D2H, PA_COPY_H2D = 0, 1, 2
+PA_SLOTS_AUTO, PA_SLOTS_SCATTERED, PA_SLOTS_RUNS = 0, 1, 2
 
 PA_OK = 0
 PA_ERR_UNSUPPORTED_HEAD_SIZE = -1
@@ -77,6 +79,7 @@ SIGNATURES = {
     "pa_multi_query_cached_kv_attention": (C.c_int, [_vp, _vp, _vp, _vp, _f32, _vp, C.POINTER(_i32), C.POINTER(_i32),
                                                      _i32, _i32, _i32, _i32, _i32, _i64, _i64, _i32, _vp, _i64, _vp]),
     "pa_reshape_and_cache": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _i64, _i64, _i32, _vp]),
+    "pa_reshape_and_cache_ex": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _i64, _i64, _i32, _i32, _vp]),
     "pa_gather_cached_kv": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _i64, _i64, _i32, _vp]),
     "pa_rotary_embedding_neox": (C.c_int, [_vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _i64, _i64, _i32, _vp]),
     "pa_rope_reshape_and_cache": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _i32, _i32,
@@ -109,6 +112,11 @@ def lib() -> C.CDLL:
                         f"{LIB_PATH} is missing: build it with `python vllm-v0.1.0_b200/build.py` "
                         "(there is no CPU or PyTorch fallback for these operators)")
                 handle = C.CDLL(LIB_PATH)
+                handle.pa_abi_version.restype = C.c_int
+                found = handle.pa_abi_version()
+                if found != PA_ABI_VERSION:
+                    raise RuntimeError(f"{LIB_PATH} reports C ABI version {found}, this binding needs {PA_ABI_VERSION}: "
+                                       "rebuild it with `python vllm-v0.1.0_b200/build.py`")
                 for name, (res, args) in SIGNATURES.items():
                     fn = getattr(handle, name)
                     fn.restype = res

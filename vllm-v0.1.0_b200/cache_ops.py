@@ -8,7 +8,7 @@ and in-place semantics; errors surface as RuntimeError.
 from __future__ import annotations
 
 import ctypes as C
-from typing import Dict, List
+from typing import Dict, List, Optional
 
 import torch
 
@@ -45,17 +45,28 @@ def _kv_rows(op: str, key: torch.Tensor, value: torch.Tensor, key_cache: torch.T
     return dev, code, num_tokens, num_heads, head_size, block_size
 
 
+_SLOT_PATTERNS = {None: _cabi.PA_SLOTS_AUTO, "scattered": _cabi.PA_SLOTS_SCATTERED, "runs": _cabi.PA_SLOTS_RUNS}
+
+
 def reshape_and_cache(key: torch.Tensor, value: torch.Tensor, key_cache: torch.Tensor, value_cache: torch.Tensor,
-                      slot_mapping: torch.Tensor) -> None:
-    """Scatter the new tokens' key/value rows into the paged caches at slot_mapping."""
+                      slot_mapping: torch.Tensor, *, slots: Optional[str] = None) -> None:
+    """Scatter the new tokens' key/value rows into the paged caches at slot_mapping.
+
+    `slots` (keyword-only, not part of the reference signature) tells the library what the caller knows about
+    slot_mapping: "scattered" = a decode step, one token per sequence, each in a block of its own; "runs" =
+    prompt tokens in consecutive slots (or a mixed batch); None = unknown.  A hint only: the result is the same."""
+    try:
+        pattern = _SLOT_PATTERNS[slots]
+    except KeyError:
+        raise RuntimeError(f"reshape_and_cache: slots must be None, 'scattered' or 'runs', not {slots!r}") from None
     ops = _cabi.torch_ops()
     if ops is not None:
-        return ops.reshape_and_cache(key, value, key_cache, value_cache, slot_mapping)
+        return ops.reshape_and_cache(key, value, key_cache, value_cache, slot_mapping, pattern)
     dev, code, n, h, d, b = _kv_rows("reshape_and_cache", key, value, key_cache, value_cache, slot_mapping)
     with torch.cuda.device(dev):
-        rc = _cabi.lib().pa_reshape_and_cache(
+        rc = _cabi.lib().pa_reshape_and_cache_ex(
             key.data_ptr(), value.data_ptr(), key_cache.data_ptr(), value_cache.data_ptr(), slot_mapping.data_ptr(),
-            n, h, d, b, key.stride(0), value.stride(0), code, torch.cuda.current_stream(dev).cuda_stream)
+            n, h, d, b, key.stride(0), value.stride(0), code, pattern, torch.cuda.current_stream(dev).cuda_stream)
     _cabi.check(rc)
 
 

@@ -371,8 +371,11 @@ template <bool kGather>
 static int scatter_gather(const void* key, const void* value, void* key_cache, void* value_cache,
                           const int32_t* slot_mapping, int32_t num_tokens, int32_t num_heads,
                           int32_t head_size, int32_t block_size, int64_t key_stride,
-                          int64_t value_stride, int32_t dtype, cudaStream_t stream) {
+                          int64_t value_stride, int32_t dtype, cudaStream_t stream,
+                          int32_t slot_pattern = PA_SLOTS_AUTO) {
   const char* op = kGather ? "gather_cached_kv" : "reshape_and_cache";
+  if (slot_pattern < PA_SLOTS_AUTO || slot_pattern > PA_SLOTS_RUNS)
+    return set_error(PA_ERR_INVALID_ARGUMENT, "%s: invalid slot pattern %d", op, slot_pattern);
   if (dtype != PA_F16 && dtype != PA_BF16 && dtype != PA_F32)
     return set_error(PA_ERR_UNSUPPORTED_DTYPE, "%s: unsupported dtype %d", op, dtype);
   if (num_tokens < 0 || num_heads <= 0 || head_size <= 0 || block_size <= 0)
@@ -406,7 +409,13 @@ static int scatter_gather(const void* key, const void* value, void* key_cache, v
   // 12.31 vs 12.32 us, 512 tokens 34.7 vs 36.7 us -- the time is the L2's: 1.3 M partial-sector stores and the
   // DRAM fills behind them, whatever issues them.  Below ~100 tokens the tile mover's head-parallel grid wins
   // (8 tokens: 4.1 vs 7.2 us, 64 tokens: 7.9 vs 8.2 us): one CTA per token cannot hide its own latency chain.
-  if (!kGather && a.vec_ok && num_tokens > kDirectMinTokens && num_tokens <= kDirectMaxTokens) {
+  // That holds for scattered slots only (a decode step).  The same token counts are also a short prompt, whose slots
+  // are consecutive: there the tile mover merges a block's tokens into whole sectors and the element sweep does not.
+  // The slot mapping lives on the device, so the host cannot tell the two apart: the caller says which it is
+  // (pa_reshape_and_cache_ex; PagedAttention knows from num_prompt_tokens), and without a hint the tile mover, which
+  // is never far off, is taken.
+  if (!kGather && a.vec_ok && slot_pattern == PA_SLOTS_SCATTERED && num_tokens > kDirectMinTokens &&
+      num_tokens <= kDirectMaxTokens) {
     if (es == 2) kv_scatter_direct_kernel<uint16_t, 512><<<num_tokens, 512, 0, stream>>>(a);
     else kv_scatter_direct_kernel<uint32_t, 512><<<num_tokens, 512, 0, stream>>>(a);
     count_launch();
@@ -807,6 +816,15 @@ int pa_reshape_and_cache(const void* key, const void* value, void* key_cache, vo
   return pa::scatter_gather<false>(key, value, key_cache, value_cache, slot_mapping, num_tokens, num_heads,
                                    head_size, block_size, key_stride, value_stride, dtype,
                                    static_cast<cudaStream_t>(stream));
+}
+
+int pa_reshape_and_cache_ex(const void* key, const void* value, void* key_cache, void* value_cache,
+                            const int32_t* slot_mapping, int32_t num_tokens, int32_t num_heads,
+                            int32_t head_size, int32_t block_size, int64_t key_stride,
+                            int64_t value_stride, int32_t dtype, int32_t slot_pattern, void* stream) {
+  return pa::scatter_gather<false>(key, value, key_cache, value_cache, slot_mapping, num_tokens, num_heads,
+                                   head_size, block_size, key_stride, value_stride, dtype,
+                                   static_cast<cudaStream_t>(stream), slot_pattern);
 }
 
 int pa_gather_cached_kv(void* key, void* value, const void* key_cache, const void* value_cache,

@@ -118,12 +118,13 @@ KvRows kv_rows(const char* op, const torch::Tensor& key, const torch::Tensor& va
 }
 
 void reshape_and_cache(torch::Tensor& key, torch::Tensor& value, torch::Tensor& key_cache, torch::Tensor& value_cache,
-                       torch::Tensor& slot_mapping) {
+                       torch::Tensor& slot_mapping, int64_t slot_pattern) {
   const KvRows r = kv_rows("reshape_and_cache", key, value, key_cache, value_cache, slot_mapping);
   const c10::cuda::CUDAGuard guard(r.dev);
-  check(pa_reshape_and_cache(key.data_ptr(), value.data_ptr(), key_cache.data_ptr(), value_cache.data_ptr(),
-                             slot_mapping.data_ptr<int>(), r.num_tokens, r.num_heads, r.head_size, r.block_size,
-                             key.stride(0), value.stride(0), r.code, stream_of(r.dev)));
+  check(pa_reshape_and_cache_ex(key.data_ptr(), value.data_ptr(), key_cache.data_ptr(), value_cache.data_ptr(),
+                                slot_mapping.data_ptr<int>(), r.num_tokens, r.num_heads, r.head_size, r.block_size,
+                                key.stride(0), value.stride(0), r.code, static_cast<int32_t>(slot_pattern),
+                                stream_of(r.dev)));
 }
 
 void gather_cached_kv(torch::Tensor& key, torch::Tensor& value, torch::Tensor& key_cache, torch::Tensor& value_cache,
@@ -284,7 +285,9 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
         py::arg("context_lens"), py::arg("block_size"), py::arg("max_context_len"), py::arg("variant") = 0,
         py::arg("num_warps") = 0, py::arg("num_stages") = 0, py::arg("num_splits") = 0,
         "Paged decode attention (replaces attention_ops.single_query_cached_kv_attention)");
-  m.def("reshape_and_cache", &reshape_and_cache, "Scatter new K/V rows into the paged caches");
+  m.def("reshape_and_cache", &reshape_and_cache, py::arg("key"), py::arg("value"), py::arg("key_cache"),
+        py::arg("value_cache"), py::arg("slot_mapping"), py::arg("slot_pattern") = 0,
+        "Scatter new K/V rows into the paged caches");
   m.def("gather_cached_kv", &gather_cached_kv, "Gather K/V rows out of the paged caches");
   m.def("copy_blocks", &copy_blocks, "Copy-on-write of cache blocks in every layer");
   m.def("swap_blocks", &swap_blocks, py::arg("src"), py::arg("dst"), py::arg("block_mapping"), py::arg("engine") = 0,

@@ -77,8 +77,10 @@ class PagedAttention(nn.Module):
             cache_event.wait()
         num_valid_tokens = input_metadata.num_valid_tokens
         if not kv_written and num_valid_tokens > 0 and key_cache is not None and value_cache is not None:
+            # a pure decode step writes one token per sequence, each into a block of its own; prompts fill runs of slots
             cache_ops.reshape_and_cache(key[:num_valid_tokens], value[:num_valid_tokens], key_cache, value_cache,
-                                        input_metadata.slot_mapping)
+                                        input_metadata.slot_mapping,
+                                        slots="scattered" if num_prompt_tokens == 0 else "runs")
         if input_metadata.num_generation_tokens > 0:
             assert key_cache is not None and value_cache is not None, \
                 "key_cache and value_cache must be provided when generating tokens."
