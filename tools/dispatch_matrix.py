@@ -5,6 +5,8 @@
 reference's own kernel (oracle/_ref, compiled unmodified for sm_100) on the same tensors.
 
     python tools/dispatch_matrix.py [--seqs 256 --heads 32 --ctx 1024]  -> gpurun_out/dispatch_matrix.json
+    python tools/dispatch_matrix.py --cells fp16:8:64,fp32:32:128 --tunings 2.4.2,2.3.2,1.8.1 [--no-ref]
+        only these cells (dtype:block:head), each under every forced launch shape (variant.warps.stages) too
 
 Per cell: ours_us / ours_gbs (algorithmic bytes of SURVEY.md section 8(d) over device time), frac_of_8tbs,
 reference_kernel_gbs, speedup, the automatic plan, and the largest difference between the two outputs.
@@ -44,13 +46,21 @@ def main():
     ap.add_argument("--seqs", type=int, default=256)
     ap.add_argument("--heads", type=int, default=32)
     ap.add_argument("--ctx", type=int, default=1024)
+    ap.add_argument("--cells", default="", help="dtype:block:head,... (default: all 36)")
+    ap.add_argument("--tunings", default="", help="variant.warps.stages,... timed beside the automatic plan")
+    ap.add_argument("--no-ref", action="store_true")
     ap.add_argument("--out", default=os.path.join(ROOT, "gpurun_out", "dispatch_matrix.json"))
     a = ap.parse_args()
-    ref = load_ref()
+    from vllm_b200 import _cabi
+    ref = None if a.no_ref else load_ref()
     rows = []
+    only = [tuple(c.split(":")) for c in a.cells.split(",") if c]
+    tunings = [tuple(int(x) for x in t.split(".")) for t in a.tunings.split(",") if t]
     for dt in ("fp16", "bf16", "fp32"):
         for B in (8, 16, 32):
             for D in (64, 80, 96, 128):
+                if only and (dt, str(B), str(D)) not in only:
+                    continue
                 wl = dict(heads=a.heads, head_size=D, block_size=B, seqs=a.seqs, ctx=a.ctx, dtype=dt)
                 p = bench.make_problem(wl, a.heads, DEV)
                 es = p["kc"].element_size()
@@ -64,6 +74,18 @@ def main():
                 row = dict(dtype=dt, block_size=B, head_size=D, page_bytes=D * B * es, ours_us=round(ms * 1e3, 1),
                            ours_gbs=round(nbytes / ms / 1e6, 1), frac_of_8tbs=round(nbytes / ms / 1e6 / 8000, 3),
                            plan=[plan.variant, plan.num_warps, plan.num_stages, plan.num_splits])
+                forced = {}
+                for (v, w, st) in tunings:
+                    tun = _cabi.DecodeTuning(v, w, st, 1)
+                    try:
+                        fms = time_gpu_only(lambda: attention_ops.single_query_cached_kv_attention(
+                            out_a, p["q"], p["kc"], p["vc"], p["scale"], p["tables"], p["lens"], B, a.ctx, tuning=tun),
+                            iters=20, warm=3)
+                        forced[f"{v}.{w}.{st}"] = round(nbytes / fms / 1e6, 1)
+                    except RuntimeError as e:
+                        forced[f"{v}.{w}.{st}"] = str(e)[:60]
+                if forced:
+                    row["forced_gbs"] = forced
                 if ref is not None and p["kc"].numel() < 2 ** 31:
                     theirs = lambda: ref.single_query_cached_kv_attention(
                         out_b, p["q"], p["kc"], p["vc"], p["scale"], p["tables"], p["lens"], B, a.ctx)

@@ -233,12 +233,15 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant
     mbar_expect_tx(bar_cf + 8 * slot, 16);
     tc05::clc_try_cancel(sClc + 16 * slot, bar_cf + 8 * slot);
   };
-  auto next_item = [&](int n, Item& it, bool arrive) {
+  // whole_warp: all 32 lanes call together and lane 0 alone arrives for them -- it may do so only once every lane
+  // has read the slot, or the scheduler could overwrite it under a lane that is still reading.
+  auto next_item = [&](int n, Item& it, bool arrive, bool whole_warp = false) {
     const uint32_t slot = n & 1;
     mbar_wait(bar_cf + 8 * slot, (n >> 1) & 1);
     int bx, by;
     const bool ok = tc05::clc_read(sClc + 16 * slot, bx, by);
     tc05::fence_async_smem();                     // my read is ordered before the slot's next asynchronous write
+    if (whole_warp) __syncwarp();
     if (arrive) mbar_arrive(bar_ce + 8 * slot);
     if (ok) it = decode(bx, by);
     return ok;
@@ -389,7 +392,7 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant
           if (lane == 0) mbar_arrive(bar_vf + 8 * s);
         }
       }
-      if (!next_item(n, it, lane == 0)) break;
+      if (!next_item(n, it, lane == 0, true)) break;
     }
   } else if (warp == 8) {
     // ===================== TMA producer =====================
@@ -544,7 +547,7 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant
       cs[0] += nA;
       cs[1] += nB;
       cB = cB_next;
-      if (!next_item(n, it, lane == 0)) break;
+      if (!next_item(n, it, lane == 0, true)) break;
     }
     // the last commits must have landed in this CTA's shared memory before the CTA may exit
     mbar_wait(bar_ve + 8 * ((g0 - 1) & 1), ((g0 - 1) >> 1) & 1);
@@ -577,7 +580,7 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant
           __syncwarp();
         }
       }
-      if (!next_item(n, it, lane == 0)) break;
+      if (!next_item(n, it, lane == 0, true)) break;
     }
   } else if (warp >= 10) {
     // register donors.  384 threads x 168 registers is the CTA's pool = 128 x 56 + 256 x 224; setmaxnreg must be
@@ -755,6 +758,10 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant
           }
           ws[128 * DP + r] = m_run;
           ws[128 * DP + 128 + r] = l_run;
+          // every warp of the group is past its bar_bl wait before row 0's thread passes the turn on: bar_bl tells
+          // its phases apart by parity only, and B's arrival for the NEXT item must not come while a warp of A still
+          // waits for this one (the whole-item path below has the same barrier ahead of its stores)
+          named_sync_n(3 + grp, 128);
         } else {
         const int D = p.head_size;
         const float inv = 1.f / l_run;
