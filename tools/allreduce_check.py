@@ -112,7 +112,7 @@ def run_leg(rank, world, dtypes=(torch.bfloat16,), hidden=5120, max_tokens=2560,
                 us_nccl = graph_time_us(lambda: dist.all_reduce(x))
                 if rank == 0:
                     nbytes = tokens * hidden * x.element_size()
-                    row = {"dtype": str(dtype).split(".")[-1], "path": "multimem (NVLS)" if mm else "peer loads/stores",
+                    row = {"dtype": str(dtype).split(".")[-1], "path": "multimem (NVLS)" if ar.path_for(nbytes) == "multimem" else "peer loads/stores",
                            "multimem": mm, "tokens": tokens, "bytes": nbytes,
                            "world": world, "correct_and_identical_on_all_ranks": ok_all, "ours_us": round(us_ours, 2),
                            "nccl_us": round(us_nccl, 2), "speedup_vs_nccl": round(us_nccl / us_ours, 2),

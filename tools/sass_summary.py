@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """Counts the Blackwell-specific SASS mnemonics per kernel of lib/libpaged_b200.so (cuobjdump -sass; no GPU needed).
 
-    python tools/sass_summary.py > profiles/r2_sass_summary.txt
+    python tools/sass_summary.py > profiles/r3_sass_summary.txt
 
 UTCHMMA = tcgen05.mma, LDTM / STTM = tcgen05.ld / .st (tensor memory), UTMALDG = TMA tensor load, UBLKCP = cp.async.bulk
 (TMA engine, no tensor map), SYNCS = mbarrier, LDGMC = multimem.ld_reduce / REDG-style multicast, FHFMA = fp16/bf16 x

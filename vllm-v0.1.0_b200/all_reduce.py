@@ -27,11 +27,16 @@ _ALL_REDUCE_LAUNCHER: Optional["GraphAllReduce"] = None
 class GraphAllReduce:
 
     def __init__(self, max_num_tokens: int, hidden_size: int, dtype: torch.dtype, disable_graph: bool = False,
-                 group=None, use_multimem: Optional[bool] = None) -> None:
+                 group=None, use_multimem: Optional[bool] = None,
+                 two_rank_peer_threshold_bytes: int = 4 << 20) -> None:
+        # two_rank_peer_threshold_bytes: with two ranks and use_multimem=None, messages larger than this take the peer
+        # path although a multicast mapping exists (one box, two sizes: 26 MB 54 us peer vs 86 us multimem, 2.6 MB
+        # equal -- the crossover has not been swept, hence a parameter); path_for() reports the choice
         import torch.distributed as dist
         self.max_num_tokens = max_num_tokens
         self.hidden_size = hidden_size
         self.disable_graph = disable_graph
+        self.two_rank_peer_threshold_bytes = two_rank_peer_threshold_bytes
         self.world_size = dist.get_world_size(group) if dist.is_initialized() else 1
         if self.world_size == 1:
             return
@@ -61,6 +66,16 @@ class GraphAllReduce:
         self.multicast_ptr = mc if use_multimem else 0
         self._code = _dtype_code(self.buffer)
 
+    def path_for(self, nbytes: int) -> str:
+        """"multimem" (reduction inside the NVSwitch) or "peer" (16-byte peer loads summed in rank order) for a message
+        of nbytes.  Every rank derives the same answer from the same arguments."""
+        if self.world_size == 1 or not self.multicast_ptr:
+            return "peer"
+        # two ranks, large message: reading the one peer directly beats the round trip through the switch's reduction
+        if self.world_size == 2 and nbytes > self.two_rank_peer_threshold_bytes and not self._forced_multimem:
+            return "peer"
+        return "multimem"
+
     def launch(self, x: torch.Tensor) -> torch.Tensor:
         # NOTE: x must be a slice of self.buffer (parallel_state.py:550)
         if self.world_size == 1:
@@ -70,11 +85,7 @@ class GraphAllReduce:
                 or not x.is_contiguous():
             raise RuntimeError("GraphAllReduce.launch: x must be a contiguous slice of self.buffer")
         stream = torch.cuda.current_stream(x.device).cuda_stream
-        # two ranks, large message: reading the one peer directly beats the round trip through the switch's
-        # reduction (measured on 2 x B200, 26 MB: 54 us peer vs 86 us multimem; 2.6 MB: equal)
-        mc = self.multicast_ptr
-        if self.world_size == 2 and x.numel() * x.element_size() > (4 << 20) and not self._forced_multimem:
-            mc = 0
+        mc = self.multicast_ptr if self.path_for(x.numel() * x.element_size()) == "multimem" else 0
         rc = _cabi.lib().pa_allreduce(self._bufs, self._flag_ptrs, mc or None, offset, x.numel(),
                                       self.rank, self.world_size, self._code, stream)
         _cabi.check(rc)
