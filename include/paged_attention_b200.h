@@ -124,7 +124,10 @@ PA_API int pa_stream_read_probe(const void* src, int64_t bytes, int32_t ctas_per
  *                  worker.py:191 computes it.  The page walk is capped by the
  *                  schedule derived from it, so a sequence longer than
  *                  max_context_len would lose its tail tokens without an error
- *                  (context_lens lives on the device; the host cannot check).
+ *                  (context_lens lives on the device; the host cannot check --
+ *                  unless PA_DEBUG_CHECKS=1 is set in the environment, which reads
+ *                  context_lens back on every call, synchronising the stream, and
+ *                  returns PA_ERR_INVALID_ARGUMENT instead).
  *
  * head_size in {64, 80, 96, 128}, block_size in {8, 16, 32}, any pa_dtype --
  * the reference's dispatch set (attention_kernels.cu:370-400, 416-448,

@@ -15,6 +15,7 @@ import cases
 import pa_testing as pt
 
 pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 GOLD = os.path.join(os.path.dirname(__file__), "golden")
 DEV = "cuda:0"
@@ -249,3 +250,26 @@ def test_shape_and_dtype_errors_surface_as_runtime_error():
         attention_ops.single_query_cached_kv_attention(out.double(), p.query.double(), p.key_cache.double(),
                                                        p.value_cache.double(), 0.1, p.block_tables, p.context_lens,
                                                        16, 20)
+
+
+def test_debug_checks_catch_a_context_longer_than_max_context_len():
+    """PA_DEBUG_CHECKS=1 turns the documented silent case (max_context_len < max(context_lens): tail tokens dropped) into
+    an error.  The switch is read once per process, so the check runs in a child."""
+    import os
+    import subprocess
+    import sys
+    code = (
+        "import sys, torch\n"
+        f"sys.path[:0] = [{ROOT!r}, {os.path.join(ROOT, 'tests')!r}]\n"
+        "import pa_testing as pt\n"
+        "p = pt.make_decode_problem(3, 2, 64, 16, 64, torch.float16, [40, 100, 7], seed=1).to('cuda')\n"
+        "pt.run_decode(p)\n"                       # max_context_len = 100: fine
+        "p.max_context_len = 64\n"
+        "try:\n"
+        "    pt.run_decode(p)\n"
+        "except RuntimeError as e:\n"
+        "    assert 'context_lens[1] = 100' in str(e), e\n"
+        "    print('CAUGHT')\n")
+    env = dict(os.environ, PA_DEBUG_CHECKS="1")
+    r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, env=env, timeout=300)
+    assert r.returncode == 0 and "CAUGHT" in r.stdout, r.stdout + r.stderr

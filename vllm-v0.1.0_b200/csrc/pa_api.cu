@@ -67,9 +67,11 @@ static int get_workspace(cudaStream_t stream, size_t ticket_bytes, size_t part_b
   Workspace& w = g_ws[std::make_pair(dev, stream)];
   ticket_bytes = (ticket_bytes + 255) / 256 * 256;
   part_bytes = (part_bytes + 255) / 256 * 256;
-  if (w.ticket_bytes < ticket_bytes || w.bytes - w.ticket_bytes < part_bytes) {
-    cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
-    PA_CUDA_TRY(cudaStreamIsCapturing(stream, &cap));
+  // the capture status is asked for at most once per call: when the buffer must grow, or while no capture has used it yet
+  cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+  const bool must_grow = w.ticket_bytes < ticket_bytes || w.bytes - w.ticket_bytes < part_bytes;
+  if (must_grow || !w.in_graph) PA_CUDA_TRY(cudaStreamIsCapturing(stream, &cap));
+  if (must_grow) {
     if (cap != cudaStreamCaptureStatusNone)
       return set_error(PA_ERR_INVALID_ARGUMENT,
                        "decode scratch must grow (%zu B) while the stream is being captured: call "
@@ -91,10 +93,7 @@ static int get_workspace(cudaStream_t stream, size_t ticket_bytes, size_t part_b
     PA_CUDA_TRY(cudaMemsetAsync(w.ptr, 0, w.ticket_bytes, stream));
     w.dirty = false;
   }
-  if (!w.in_graph) {
-    cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
-    if (cudaStreamIsCapturing(stream, &cap) == cudaSuccess && cap != cudaStreamCaptureStatusNone) w.in_graph = true;
-  }
+  if (cap != cudaStreamCaptureStatusNone) w.in_graph = true;
   *tickets = static_cast<uint32_t*>(w.ptr);
   *parts = reinterpret_cast<float*>(static_cast<char*>(w.ptr) + w.ticket_bytes);
   return PA_OK;
@@ -187,9 +186,26 @@ static int make_plan(int num_seqs, int num_heads, int head_size, int block_size,
   if (t->num_warps <= 0) {
     t->num_warps = max_pages <= 4 ? 1 : (max_pages <= 8 ? 2 : 4);
     while (staged && t->num_warps > 1 && t->num_warps * 2 * stage > 160 * 1024) t->num_warps >>= 1;
+    // 16 KiB pages (fp32, block 32, head 128): two warps' ring already takes more than half an SM, so one CTA is
+    // resident either way -- a third warp raises the bytes in flight from 128 to 192 KiB (5.4 -> 7.1 TB/s)
+    if (staged && t->num_warps == 2 && 2 * 2 * stage > 113 * 1024 && 3 * 2 * stage <= 200 * 1024) t->num_warps = 3;
+    // 8 KiB pages of 32 tokens, fp32 (head 64): 4 warps x 2 stages is one CTA of 128 KiB per SM; CTAs of two warps fit
+    // three times (192 KiB in flight): 6.96 -> 7.46 TB/s.  The 16-bit twin (head 128) keeps its four warps, which the
+    // sibling-group path needs, and gets a third stage instead (below).
+    if (staged && t->num_warps == 4 && block_size == 32 && page == 8192 && dtype == PA_F32) t->num_warps = 2;
   }
   if (t->num_warps > 8) t->num_warps = 8;
-  if (t->num_stages <= 0) t->num_stages = 2;
+  if (t->num_stages <= 0) {
+    // All rules measured over the reference's dispatch set at 256 x 32 x 1024 (profiles/r3_dispatch_tune.json).
+    // Two stages per warp, except:
+    //  * pages under 2 KiB (block 8 with head 64 / 80 / 96 in 16 bits): a warp is through such a page long before the
+    //    next copy lands, and two stages leave it waiting -- 8 KiB in flight per warp: 4.6 -> 7.1 TB/s (head 64, four
+    //    stages), 5.9 -> 7.3 (head 96, three);
+    //  * 8 KiB pages of 32 tokens in 16 bits: one CTA per SM, a third stage brings 192 KiB in flight: 7.19 -> 7.39.
+    t->num_stages = 2;
+    if (staged && stage < 4096) t->num_stages = (8192 + stage - 1) / stage;
+    if (staged && auto_warps && t->num_warps == 4 && block_size == 32 && page == 8192 && dtype != PA_F32) t->num_stages = 3;
+  }
   if (!staged) t->num_stages = 1;
   if (t->num_stages > 32) t->num_stages = 32;
   // Just over one wave of short items (444 < items <= 1.25 x 444 at 4 warps, <= 64 pages): the second wave
@@ -295,6 +311,24 @@ static int decode(void* out, const void* query, const void* key_cache, const voi
     if (rc != PA_OK) return rc;
   }
   if (reserve_only) return PA_OK;
+  // PA_DEBUG_CHECKS=1 (read once per process): the one contract the host cannot normally verify, max_context_len >=
+  // max(context_lens) -- a longer sequence would silently lose its tail tokens -- is checked by reading context_lens
+  // back.  This synchronises the stream on every call: a debugging aid, skipped while the stream is being captured.
+  static const bool debug_checks = [] { const char* e = getenv("PA_DEBUG_CHECKS"); return e && e[0] == '1'; }();
+  if (debug_checks) {
+    cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+    PA_CUDA_TRY(cudaStreamIsCapturing(stream, &cap));
+    if (cap == cudaStreamCaptureStatusNone) {
+      std::vector<int32_t> lens(num_seqs);
+      PA_CUDA_TRY(cudaMemcpyAsync(lens.data(), context_lens, sizeof(int32_t) * num_seqs, cudaMemcpyDeviceToHost, stream));
+      PA_CUDA_TRY(cudaStreamSynchronize(stream));
+      for (int i = 0; i < num_seqs; ++i)
+        if (lens[i] > max_context_len || lens[i] < 0)
+          return set_error(PA_ERR_INVALID_ARGUMENT, "context_lens[%d] = %d is outside [0, max_context_len = %d]: the "
+                           "page walk is sized from max_context_len (worker.py:191 passes the maximum)", i, lens[i],
+                           max_context_len);
+    }
+  }
   l.num_seqs = num_seqs; l.head_size = head_size; l.block_size = block_size;
   l.num_warps = t.num_warps; l.staged = (t.variant >= 2); l.stream = stream;
   static const bool pdl = [] { const char* e = getenv("PA_DECODE_PDL"); return !(e && e[0] == '0'); }();
