@@ -168,7 +168,8 @@ constexpr int kMaxPagesPerSplit = 8192;  // block-table slice kept in shared mem
 // Fills the zero fields of `t`.  Returns pages_per_split through the pointer.
 //
 // The rules come from sweeps on B200 (profiles/r1_sweep_*.json):
-//   * two ring stages per warp everywhere: deeper rings only cost resident CTAs;
+//   * two ring stages per warp, deeper rings only cost resident CTAs -- except for the page sizes listed at
+//     num_stages below (round 3: profiles/r3_dispatch_tune.json);
 //   * warps per CTA follow the pages one (sequence, head) has: a warp wants >= 4 pages,
 //     and short contexts run best as many small CTAs (W = 1: 14 resident CTAs per SM);
 //   * the context is split only when the (sequence, head) items cannot occupy the
