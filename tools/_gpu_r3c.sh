@@ -1,4 +1,5 @@
 # round 3, call C: compute-sanitizer over the GPU tests of the hot path; summaries -> gpurun_out/r3_sanitizer_*.log
+# NOTE: compute-sanitizer is closed on this pool (exit 86 before the target starts); kept as the record of what was asked for.
 mkdir -p gpurun_out
 CS=/usr/local/cuda/bin/compute-sanitizer
 run() {  # tool, time limit, label, pytest args...
